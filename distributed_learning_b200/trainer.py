@@ -1,0 +1,219 @@
+"""The training loop.
+
+Parity: reference ``worker_process`` (``src/main.py:29-107``): seed 1234, dataset partition,
+model -> device -> wrapper, SGD(lr 0.01, momentum 0.5), NLL loss, ``epoch_count`` epochs cut
+off at ``limit_batches``, the eight timed phases (``get_data, data2dev, zero_grad, forward,
+backprop, sync, optimizer_step, batch``), one CSV row per batch with ``batch_count`` and
+``data_len``, and the three result files
+``{name}_config.txt``, ``{name}_{node}_{worker}_loss.txt``, ``{name}_{node}_{worker}_times.csv``.
+
+Differences, all from SURVEY.md §2.8/§7.4:
+
+* phases are timed on the device with CUDA events when the device is a GPU (Q9);
+* on a GPU the loss is *not* read back every batch (H4: for a 1 ms step the reference's
+  ``f"{loss}"`` synchronise is most of the step); losses stay on the device and the loss file
+  is written at the end.  ``--sync_loss 1`` restores the per-batch read-back;
+* ``--random_input 1`` generates batches on the device (K13); ``2`` reproduces the
+  reference's host RNG + copy; ``3`` is a pinned-host pool fed through ``PinnedPrefetcher``
+  (the end-to-end input path);
+* the wrapper may provide its own optimizer (``make_optimizer``: the fused SGD kernel);
+* checkpoint/resume (``--checkpoint``, ``--checkpoint_every``, ``--resume``);
+* initial weights are broadcast from rank 0 when a process group exists (Q13).
+"""
+from __future__ import annotations
+
+import datetime
+import os
+import sys
+import traceback
+from contextlib import nullcontext
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+import torch.optim as optim
+
+from .utils.checkpoint import load_checkpoint, save_checkpoint
+from .utils.config import picklable_config
+from .utils.data import PinnedPrefetcher, random_data_generator
+from .utils.logging import Level, print_d
+from .utils.timing import PhaseTimer
+
+
+def _is_primary(node_id: int, worker_id: int) -> bool:
+    return node_id == 0 and worker_id == 0
+
+
+def prepare_model(config, device: torch.device):
+    """Build the network on ``device`` in the configured dtype / memory format."""
+    model = config.create_network().to(device)
+    if getattr(config, "channels_last", 0) and device.type == "cuda":
+        model = model.to(memory_format=torch.channels_last)
+    model.train()
+    return model
+
+
+def broadcast_initial_state(model, group=None) -> None:
+    """Make every replica start from rank 0's parameters and buffers."""
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    net = getattr(model, "__dict__", {}).get("model", None) or model
+    backend = dist.get_backend(group)
+    with torch.no_grad():
+        for t in list(net.parameters()) + list(net.buffers()):
+            if backend == "gloo" and t.is_cuda:
+                tmp = t.detach().cpu()
+                dist.broadcast(tmp, 0, group=group)
+                t.copy_(tmp)
+            else:
+                dist.broadcast(t.detach(), 0, group=group)
+
+
+def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bool = False):
+    print_d(f"Starting experiment {config.experiment}, {datetime.datetime.now()}", Level.INFO)
+    torch.manual_seed(getattr(config, "seed", 1234))
+    device = torch.device(config.devices[worker_id])
+    on_gpu = device.type == "cuda"
+    if on_gpu:
+        torch.cuda.set_device(device)
+
+    train_set = config.get_partition_dataset(node_id, worker_id, config.node_dev, config.total_dev,
+                                             config.dataset_root, config.batch_size)
+    model = prepare_model(config, device)
+    buff_device = device if gpu_reduce else "cpu"
+    model = config.distribute_model(model, reducer, config.grouping_size, buff_device)
+
+    lr, momentum = getattr(config, "lr", 0.01), getattr(config, "momentum", 0.5)
+    if hasattr(model, "make_optimizer"):
+        optimizer = model.make_optimizer(lr=lr, momentum=momentum)
+    else:
+        optimizer = optim.SGD(model.parameters(), lr=lr, momentum=momentum)
+
+    autocast = (torch.autocast(device_type=device.type, dtype=torch.bfloat16)
+                if getattr(config, "dtype", "fp32") == "bf16" and not getattr(model, "handles_dtype", False)
+                else nullcontext())
+
+    name = config.experiment_name
+    os.makedirs(config.folder, exist_ok=True)
+    with open(f"{config.folder}/{name}_config.txt", "w") as f:
+        f.write(str(picklable_config(config)))
+
+    batch_count = 0
+    start_epoch = 0
+    ckpt = getattr(config, "checkpoint", None)
+    if ckpt and getattr(config, "resume", 0) and os.path.exists(ckpt):
+        payload = load_checkpoint(ckpt, model, optimizer, map_location="cpu")
+        batch_count, start_epoch = payload["batch_count"], payload["epoch"]
+        print_d(f"Resumed from {ckpt} at batch {batch_count}", Level.INFO)
+    else:
+        broadcast_initial_state(model, getattr(config, "worker_group", None))
+
+    timer = PhaseTimer(device, mode=getattr(config, "timer", "auto"))
+    sync_loss = bool(getattr(config, "sync_loss", 0 if on_gpu else 1))
+    pending_losses = []          # (batch_count, device scalar) when the loss is not read back per batch
+    loss_path = f"{config.folder}/{name}_{node_id}_{worker_id}_loss.txt"
+    loss_f = open(loss_path, "w")
+
+    def loss_line(k, value):
+        return f"Worker {node_id}:{worker_id} loss for batch {k}: {value}\n"
+
+    random_input = int(getattr(config, "random_input", 0))
+    every = int(getattr(config, "checkpoint_every", 0) or 0)
+    limit = config.limit_batches
+    epoch = start_epoch
+    for epoch in range(start_epoch, config.epoch_count):
+        if batch_count >= limit:
+            break
+        gener = iter(train_set)
+        if random_input:
+            first = next(gener)
+            if random_input == 1:
+                gener = random_data_generator(first, device=device if on_gpu else None)
+            elif random_input == 2:
+                gener = random_data_generator(first)
+            else:
+                gener = PinnedPrefetcher(random_data_generator(first), device,
+                                         channels_last=bool(getattr(config, "channels_last", 0)))
+        while batch_count < limit:
+            timer.start("batch")
+
+            timer.start("get_data")
+            nx = next(gener, None)
+            if nx is None:
+                break
+            data, target = nx
+            timer.end("get_data")
+
+            timer.start("data2dev")
+            data, target = data.to(device, non_blocking=True), target.to(device, non_blocking=True)
+            timer.end("data2dev")
+
+            timer.start("zero_grad")
+            optimizer.zero_grad()
+            timer.end("zero_grad")
+
+            timer.start("forward")
+            with autocast:
+                output = model(data)
+                loss = F.nll_loss(output.float() if output.dtype != torch.float32 else output, target)
+            timer.end("forward")
+
+            timer.start("backprop")
+            loss.backward()
+            timer.end("backprop")
+
+            timer.start("sync")
+            model.sync_gradients()
+            timer.end("sync")
+
+            timer.start("optimizer_step")
+            optimizer.step()
+            timer.end("optimizer_step")
+
+            if sync_loss:
+                value = loss.item()
+                print_d(loss_line(batch_count, value).rstrip(), Level.DEBUG)
+                loss_f.write(loss_line(batch_count, value))
+            else:
+                pending_losses.append((batch_count, loss.detach()))
+            timer.end("batch")
+            timer.end_step(name, {"batch_count": batch_count, "data_len": data.size(0)})
+            batch_count += 1
+
+            if ckpt and every and batch_count % every == 0 and _is_primary(node_id, worker_id):
+                save_checkpoint(ckpt, model, optimizer, batch_count, epoch, config)
+
+    if pending_losses:
+        values = torch.stack([v for _, v in pending_losses]).float().cpu().tolist()
+        for (k, _), v in zip(pending_losses, values):
+            loss_f.write(loss_line(k, v))
+    loss_f.close()
+
+    if ckpt and _is_primary(node_id, worker_id):
+        save_checkpoint(ckpt, model, optimizer, batch_count, epoch, config)
+
+    rows = timer.rows()
+    model.cleanup()
+    if reducer is not None and hasattr(reducer, "cleanup"):
+        reducer.cleanup()
+    timer.writeout(f"{config.folder}/{name}_{node_id}_{worker_id}_times.csv", rows)
+    return rows
+
+
+def worker_process_wrapper(*args):
+    """Entry point of spawned workers: report the failure and exit non-zero instead of hanging
+    the node (the reference prints and swallows, ``src/main.py:109-114``)."""
+    try:
+        worker_process(*args)
+    except Exception:
+        traceback.print_exc(file=sys.stdout)
+        sys.stdout.flush()
+        # let the node's pump see a shutdown so it does not wait forever
+        reducer = args[3] if len(args) > 3 else None
+        try:
+            if reducer is not None and hasattr(reducer, "cleanup"):
+                reducer.cleanup()
+        finally:
+            os._exit(1)
