@@ -1,0 +1,414 @@
+"""The native communicator: a peer-mapped arena per GPU and the in-kernel allreduce over it.
+
+One process per GPU.  ``NativeComm.allocate`` is collective: every rank allocates an arena of
+the same size, exports it, and maps every peer's arena (VMM allocations shared as POSIX file
+descriptors over a unix socket, with a multicast object bound on top when the box supports NVLS;
+legacy CUDA IPC handles as the fallback).  The bootstrap (token, barriers, IPC handles) goes
+through a ``torch.distributed`` group -- gloo is enough, NCCL is never needed.  Afterwards a
+fusion buffer is an ``(offset, numel, dtype)`` triple that means the same bytes in every rank's
+arena, and ``allreduce`` launches ONE kernel on the caller's stream (``csrc/allreduce.cu``).
+
+This replaces reference ``init_process`` + ``pgroups`` (``src/main.py:303-318``) and the
+``reduce_fn`` injected into the reducers (``src/main.py:131,141,210``).
+
+``emulated_allreduce`` runs N "ranks" in one cooperative launch on one GPU; it exists so the
+kernel logic (barrier, slicing, epilogue) is testable where only one GPU is available.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import uuid
+from ctypes import c_int, c_size_t, c_uint64, c_void_p
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from ._lib import (DLB_MAX_BLOCKS, DLB_MAX_RANKS, DLB_SIGNAL_BYTES, DLB_STATE_WORDS, DlbError, FusedSgd, check,
+                   dtype_code, lib, ptr_array, stream_handle)
+
+ALGOS = ("oneshot", "twoshot", "nvls")
+_ALIGN = 4096
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class _RawCudaMemory:
+    """Adapter that lets torch wrap a raw device pointer (CUDA array interface v2)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def tensor_from_ptr(ptr: int, nbytes: int, device) -> torch.Tensor:
+    """A uint8 tensor over ``[ptr, ptr+nbytes)``; the caller keeps the memory alive."""
+    return torch.as_tensor(_RawCudaMemory(ptr, nbytes), device=device)
+
+
+def default_nblocks(nbytes: int, algo: str) -> int:
+    env = os.environ.get("DLB200_NBLOCKS")
+    if env:
+        return max(1, min(DLB_MAX_BLOCKS, int(env)))
+    if nbytes <= 256 << 10:
+        return 8
+    if nbytes <= 4 << 20:
+        return 16
+    if nbytes <= 32 << 20:
+        return 32
+    return 48
+
+
+class NativeComm:
+    def __init__(self, group=None, device=None, prefer: str = "auto", nthreads: int = 512):
+        import torch.distributed as dist
+
+        self._dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if self.world > DLB_MAX_RANKS:
+            raise ValueError(f"the native backend spans one NVSwitch domain: at most {DLB_MAX_RANKS} ranks, got {self.world}")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.prefer = os.environ.get("DLB200_ARENA", prefer)          # auto | vmm | ipc
+        self.nthreads = nthreads
+        self.mode: Optional[str] = None
+        self.nbytes = 0
+        self.data_offset = _round_up(DLB_SIGNAL_BYTES, _ALIGN)
+        self.peer_ptrs: List[int] = []
+        self.mc_ptr: Optional[int] = None
+        self.local: Optional[torch.Tensor] = None
+        self.state = torch.zeros(DLB_STATE_WORDS, dtype=torch.int32, device=self.device)
+        self._sig_array = None
+        self._buf_arrays: Dict[int, "ctypes.Array"] = {}
+        self._handles: dict = {}
+        self.tuned: Dict[Tuple[int, int], Tuple[str, int]] = {}     # (dtype code, pow2 bytes) -> (algo, nblocks)
+        self.launches = 0
+
+    # ---------------------------------------------------------------------------------------
+    # bring-up
+    # ---------------------------------------------------------------------------------------
+    def _gather(self, obj):
+        out = [None] * self.world
+        self._dist.all_gather_object(out, obj, group=self.group)
+        return out
+
+    def _barrier(self):
+        if self.world > 1:
+            self._dist.barrier(group=self.group) if self._dist.get_backend(self.group) != "nccl" else \
+                self._dist.barrier(group=self.group, device_ids=[self.device.index])
+
+    def allocate(self, data_bytes: int) -> None:
+        """Collective.  Allocates signal pad + ``data_bytes`` and maps all peers."""
+        if self.mode is not None:
+            raise RuntimeError("arena already allocated")
+        total = self.data_offset + _round_up(max(data_bytes, 16), _ALIGN)
+        torch.cuda.set_device(self.device)
+        modes = {"auto": ("vmm", "ipc"), "vmm": ("vmm",), "ipc": ("ipc",)}[self.prefer]
+        err: Optional[Exception] = None
+        for mode in modes:
+            try:
+                ok_local, exc = True, None
+                try:
+                    if mode == "vmm":
+                        self._allocate_vmm(total)
+                    else:
+                        self._allocate_ipc(total)
+                except (DlbError, OSError, RuntimeError) as e:   # noqa: PERF203
+                    ok_local, exc = False, e
+                # every rank must take the same decision
+                oks = self._gather(ok_local) if self.world > 1 else [ok_local]
+                if all(oks):
+                    self.mode = mode
+                    break
+                err = exc or RuntimeError(f"arena mode {mode} failed on ranks {[i for i, o in enumerate(oks) if not o]}")
+                self._release_partial()
+            except Exception as e:  # noqa: BLE001
+                err = e
+                self._release_partial()
+        if self.mode is None:
+            raise RuntimeError(f"could not set up peer-mapped memory ({err})") from err
+        self.nbytes = total
+        self.local = tensor_from_ptr(self.peer_ptrs[self.rank], total, self.device)
+        self._sig_array = ptr_array(self.peer_ptrs)          # the signal pad sits at offset 0
+        self._barrier()
+
+    def _allocate_ipc(self, total: int) -> None:
+        L = lib()
+        p = c_void_p()
+        check(L.dlb_mem_alloc(total, ctypes.byref(p)))
+        self._handles = {"ipc_local": p.value, "ipc_peers": []}
+        handle = ctypes.create_string_buffer(64)
+        check(L.dlb_ipc_export(p, handle))
+        handles = self._gather(handle.raw) if self.world > 1 else [handle.raw]
+        ptrs = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                ptrs.append(p.value)
+            else:
+                q = c_void_p()
+                check(L.dlb_ipc_open(ctypes.create_string_buffer(h, 64), ctypes.byref(q)))
+                self._handles["ipc_peers"].append(q.value)
+                ptrs.append(q.value)
+        self.peer_ptrs = ptrs
+
+    def _allocate_vmm(self, total: int) -> None:
+        L = lib()
+        dev = self.device.index
+        h, p, rounded = c_uint64(), c_void_p(), c_size_t()
+        check(L.dlb_vmm_alloc(dev, total, ctypes.byref(h), ctypes.byref(p), ctypes.byref(rounded)))
+        self._handles = {"vmm_local": (h.value, p.value, rounded.value), "vmm_peers": []}
+        ptrs = [None] * self.world
+        ptrs[self.rank] = p.value
+        if self.world > 1:
+            token = self._gather(uuid.uuid4().hex if self.rank == 0 else None)[0]
+            name = lambda r: f"dlb200-{token}-{r}".encode()     # noqa: E731
+            lfd = c_int()
+            check(L.dlb_fd_listen(name(self.rank), ctypes.byref(lfd)))
+            try:
+                self._barrier()                                  # everyone is listening
+                fd = c_int()
+                check(L.dlb_vmm_export_fd(h.value, ctypes.byref(fd)))
+                for r in range(self.world):
+                    if r != self.rank:
+                        check(L.dlb_fd_send(name(r), fd.value, self.rank, 30000))
+                L.dlb_fd_close(fd.value)
+                for _ in range(self.world - 1):
+                    pfd, tag = c_int(), c_int()
+                    check(L.dlb_fd_accept(lfd.value, ctypes.byref(pfd), ctypes.byref(tag), 30000))
+                    ph, pp = c_uint64(), c_void_p()
+                    check(L.dlb_vmm_import_fd(pfd.value, ctypes.byref(ph)))
+                    L.dlb_fd_close(pfd.value)
+                    check(L.dlb_vmm_map(dev, ph.value, rounded.value, ctypes.byref(pp)))
+                    self._handles["vmm_peers"].append((ph.value, pp.value, rounded.value))
+                    ptrs[tag.value] = pp.value
+                self._barrier()
+                self._setup_multicast(L, dev, lfd.value, name, h.value, rounded.value)
+            finally:
+                L.dlb_fd_close(lfd.value)
+        self.peer_ptrs = ptrs
+
+    def _setup_multicast(self, L, dev: int, lfd: int, name, mem_handle: int, rounded: int) -> None:
+        """NVLS: bind every rank's arena to one multicast object.  Optional: any failure leaves
+        ``mc_ptr`` unset on all ranks and the nvls variant unavailable."""
+        if os.environ.get("DLB200_NO_MULTICAST"):
+            sup = False
+        else:
+            yes = c_int()
+            sup = L.dlb_mc_supported(dev, ctypes.byref(yes)) == 0 and bool(yes.value)
+        if not all(self._gather(sup)):
+            return
+        mc = c_uint64()
+        step_ok = True
+        try:
+            if self.rank == 0:
+                mrounded = c_size_t()
+                check(L.dlb_mc_create(self.world, rounded, ctypes.byref(mc), ctypes.byref(mrounded)))
+                if mrounded.value != rounded:
+                    raise RuntimeError("multicast granularity differs from the arena's")
+                fd = c_int()
+                check(L.dlb_vmm_export_fd(mc.value, ctypes.byref(fd)))
+                for r in range(1, self.world):
+                    check(L.dlb_fd_send(name(r), fd.value, 1000, 30000))
+                L.dlb_fd_close(fd.value)
+            else:
+                pfd, tag = c_int(), c_int()
+                check(L.dlb_fd_accept(lfd, ctypes.byref(pfd), ctypes.byref(tag), 30000))
+                check(L.dlb_vmm_import_fd(pfd.value, ctypes.byref(mc)))
+                L.dlb_fd_close(pfd.value)
+            check(L.dlb_mc_add_device(mc.value, dev))
+        except (DlbError, RuntimeError):
+            step_ok = False
+        if not all(self._gather(step_ok)):      # also the "all devices added" barrier
+            return
+        try:
+            check(L.dlb_mc_bind(mc.value, 0, mem_handle, rounded))
+            mp = c_void_p()
+            check(L.dlb_mc_map(dev, mc.value, rounded, ctypes.byref(mp)))
+        except DlbError:
+            step_ok = False
+        if all(self._gather(step_ok)):
+            self.mc_ptr = mp.value
+            self._handles["mc"] = (mc.value, mp.value, rounded)
+
+    def _release_partial(self) -> None:
+        self.peer_ptrs, self.mc_ptr, self._handles = [], None, {}
+
+    @property
+    def has_multicast(self) -> bool:
+        return self.mc_ptr is not None
+
+    # ---------------------------------------------------------------------------------------
+    # buffers
+    # ---------------------------------------------------------------------------------------
+    def view(self, offset: int, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        """Local tensor over ``numel`` elements at data offset ``offset`` (bytes, 16-aligned)."""
+        esize = torch.empty((), dtype=dtype).element_size()
+        lo = self.data_offset + offset
+        if offset % 16 or lo + numel * esize > self.nbytes:
+            raise ValueError("arena view out of range or misaligned")
+        return self.local[lo:lo + numel * esize].view(dtype)
+
+    def _bufs(self, offset: int):
+        arr = self._buf_arrays.get(offset)
+        if arr is None:
+            base = self.data_offset + offset
+            arr = ptr_array([p + base for p in self.peer_ptrs])
+            self._buf_arrays[offset] = arr
+        return arr
+
+    # ---------------------------------------------------------------------------------------
+    # collectives
+    # ---------------------------------------------------------------------------------------
+    def choose(self, nbytes: int, dtype: torch.dtype, algo: str = "auto") -> Tuple[str, int]:
+        """Variant and grid for a message: the measured table if ``tune`` filled it, else a
+        size heuristic (one-shot while latency dominates, NVLS when the switch can reduce)."""
+        if algo != "auto":
+            if algo == "nvls" and not self.has_multicast:
+                algo = "twoshot"
+            return algo, default_nblocks(nbytes, algo)
+        key = (dtype_code(dtype), max(nbytes, 1).bit_length())
+        if key in self.tuned:
+            return self.tuned[key]
+        if nbytes <= (256 << 10) * 8 // max(self.world, 2):
+            return "oneshot", default_nblocks(nbytes, "oneshot")
+        if self.has_multicast:
+            return "nvls", default_nblocks(nbytes, "nvls")
+        return "twoshot", default_nblocks(nbytes, "twoshot")
+
+    def allreduce(self, offset: int, numel: int, dtype: torch.dtype, algo: str = "twoshot", scale: float = 1.0,
+                  out_offset: Optional[int] = None, sgd: Optional[FusedSgd] = None, nblocks: Optional[int] = None,
+                  stream=None) -> None:
+        """Sum ``numel`` elements at ``offset`` over all ranks (times ``scale``) on ``stream``.
+
+        two-shot / nvls work in place; one-shot writes to ``out_offset`` (no trailing barrier:
+        the caller alternates input buffers between consecutive uses).  ``sgd`` fuses the
+        parameter update.  Every rank must make the same sequence of calls."""
+        L = lib()
+        esize = torch.empty((), dtype=dtype).element_size()
+        nblocks = nblocks or default_nblocks(numel * esize, algo)
+        sgd_p = ctypes.byref(sgd) if sgd is not None else None
+        st = stream_handle(stream)
+        code = dtype_code(dtype)
+        if algo == "twoshot":
+            check(L.dlb_allreduce_twoshot(self._bufs(offset), self._sig_array, self.state.data_ptr(), self.rank,
+                                          self.world, numel, code, scale, nblocks, self.nthreads, sgd_p, st))
+        elif algo == "oneshot":
+            if out_offset is None and sgd is None:
+                raise ValueError("one-shot needs out_offset (it cannot work in place)")
+            out = self.peer_ptrs[self.rank] + self.data_offset + out_offset if out_offset is not None else None
+            check(L.dlb_allreduce_oneshot(self._bufs(offset), out, self._sig_array, self.state.data_ptr(), self.rank,
+                                          self.world, numel, code, scale, nblocks, self.nthreads, 0, sgd_p, st))
+        elif algo == "nvls":
+            if not self.has_multicast:
+                raise RuntimeError("nvls requested but no multicast mapping exists")
+            check(L.dlb_allreduce_nvls(self.mc_ptr + self.data_offset + offset, self._bufs(offset), self._sig_array,
+                                       self.state.data_ptr(), self.rank, self.world, numel, code, scale, nblocks,
+                                       self.nthreads, sgd_p, st))
+        else:
+            raise ValueError(f"unknown algo {algo!r}")
+        self.launches += 1
+
+    def barrier(self, stream=None, nblocks: int = 1) -> None:
+        check(lib().dlb_barrier(self._sig_array, self.state.data_ptr(), self.rank, self.world, nblocks, stream_handle(stream)))
+        self.launches += 1
+
+    def check(self, stream=None) -> None:
+        """Raise if a device-side wait timed out (synchronises ``stream``)."""
+        check(lib().dlb_comm_check(self.state.data_ptr(), stream_handle(stream)))
+
+    # ---------------------------------------------------------------------------------------
+    # measured selection
+    # ---------------------------------------------------------------------------------------
+    def tune(self, sizes_bytes: Sequence[int], dtype: torch.dtype = torch.float32, iters: int = 10,
+             scratch_offset: int = 0, block_choices: Sequence[int] = (8, 16, 32, 48)) -> Dict[int, dict]:
+        """Collective.  Time every available variant (and grid) on each size, take the max over
+        ranks, and remember the fastest per size class.  Uses arena bytes
+        ``[scratch_offset, scratch_offset + 2*max(sizes))``; contents are destroyed."""
+        esize = torch.empty((), dtype=dtype).element_size()
+        stream = torch.cuda.current_stream(self.device)
+        report: Dict[int, dict] = {}
+        algos = [a for a in ALGOS if a != "nvls" or self.has_multicast]
+        for nbytes in sizes_bytes:
+            nbytes = _round_up(nbytes, 16)
+            numel = nbytes // esize
+            out_off = scratch_offset + _round_up(nbytes, _ALIGN)
+            results = {}
+            for algo in algos:
+                if algo == "oneshot" and nbytes * self.world > 256 << 20:
+                    continue
+                for nb in block_choices:
+                    def run():
+                        self.allreduce(scratch_offset, numel, dtype, algo, 1.0, out_offset=out_off, nblocks=nb, stream=stream)
+                    for _ in range(2):
+                        run()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(stream)
+                    for _ in range(iters):
+                        run()
+                    e1.record(stream)
+                    e1.synchronize()
+                    results[(algo, nb)] = e0.elapsed_time(e1) / iters
+            keys = sorted(results)
+            t = torch.tensor([results[k] for k in keys], dtype=torch.float64)
+            if self.world > 1:
+                if self._dist.get_backend(self.group) == "nccl":
+                    t = t.to(self.device)
+                self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX, group=self.group)
+                t = t.cpu()
+            best = int(torch.argmin(t))
+            self.tuned[(dtype_code(dtype), max(nbytes, 1).bit_length())] = keys[best]
+            report[nbytes] = {"best": keys[best], "ms": {f"{a}/{b}": float(v) for (a, b), v in zip(keys, t.tolist())}}
+        return report
+
+    def close(self) -> None:
+        if self.mode is None:
+            return
+        torch.cuda.synchronize(self.device)
+        self._barrier()
+        L = lib()
+        self.local = None
+        h = self._handles
+        if self.mode == "ipc":
+            for p in h.get("ipc_peers", []):
+                L.dlb_ipc_close(p)
+            self._barrier()
+            L.dlb_mem_free(h["ipc_local"])
+        else:
+            if "mc" in h:
+                mc, mp, size = h["mc"]
+                L.dlb_vmm_unmap(mp, size)
+                L.dlb_vmm_release(mc)
+            for ph, pp, size in h.get("vmm_peers", []):
+                L.dlb_vmm_unmap(pp, size)
+                L.dlb_vmm_release(ph)
+            self._barrier()
+            lh, lp, size = h["vmm_local"]
+            L.dlb_vmm_unmap(lp, size)
+            L.dlb_vmm_release(lh)
+        self.mode = None
+        self._handles = {}
+
+
+# ---------------------------------------------------------------------------------------------
+# single-GPU emulation (tests)
+# ---------------------------------------------------------------------------------------------
+def emulated_flags(nranks: int, device) -> torch.Tensor:
+    """Zeroed scratch for ``emulated_allreduce``; reuse it across calls (epochs only grow)."""
+    return torch.zeros(lib().dlb_emulated_flags_bytes(nranks), dtype=torch.uint8, device=device)
+
+
+def emulated_allreduce(bufs: Sequence[torch.Tensor], algo: str = "twoshot", scale: float = 1.0,
+                       outs: Optional[Sequence[torch.Tensor]] = None, sgds: Optional[Sequence[FusedSgd]] = None,
+                       flags: Optional[torch.Tensor] = None, nblocks: int = 4, nthreads: int = 256, stream=None) -> None:
+    """All ``len(bufs)`` ranks in one cooperative launch on one GPU (see ``dlb200.h``)."""
+    n = len(bufs)
+    if flags is None:
+        flags = emulated_flags(n, bufs[0].device)
+    B = ptr_array([b.data_ptr() for b in bufs])
+    O = ptr_array([o.data_ptr() for o in outs]) if outs is not None else None
+    S = (FusedSgd * n)(*sgds) if sgds is not None else None
+    check(lib().dlb_allreduce_emulated({"twoshot": 0, "oneshot": 1}[algo], B, O, S, flags.data_ptr(), n,
+                                       bufs[0].numel(), dtype_code(bufs[0].dtype), scale, nblocks, nthreads,
+                                       stream_handle(stream)))

@@ -62,7 +62,8 @@ class Bucket:
     """
 
     def __init__(self, bucket_id: int, tensors: Sequence[torch.Tensor], device="cpu",
-                 dtype: Optional[torch.dtype] = None, buffer: Optional[torch.Tensor] = None, aligned: bool = False):
+                 dtype: Optional[torch.dtype] = None, buffer: Optional[torch.Tensor] = None, aligned: bool = False,
+                 allocate: bool = True):
         self.bucket_id = bucket_id
         self.tensors = list(tensors)
         self.dtype = dtype or self.tensors[0].dtype
@@ -75,11 +76,12 @@ class Bucket:
             cur = _round_up(cur + t.numel(), step)
         self.numel = cur
         self.dense_numel = sum(t.numel() for t in self.tensors)
-        if buffer is None:
+        if buffer is None and allocate:
             buffer = torch.zeros(self.numel, dtype=self.dtype, device=device)
-        elif buffer.numel() < self.numel:
+        elif buffer is not None and buffer.numel() < self.numel:
             raise ValueError("bucket buffer too small")
-        self.grad_buffer = buffer[: self.numel]
+        # allocate=False: layout only; the owner assigns grad_buffer later (native arena)
+        self.grad_buffer = buffer[: self.numel] if buffer is not None else None
         self.ready = 0
 
     @property

@@ -1,0 +1,426 @@
+"""``B200Dist``: the native data-parallel wrapper, and ``FusedSGD``, its optimizer.
+
+Parity: the wrapper surface of reference ``OurDist`` / ``SeqMergeDist`` (``src/ourdist.py:53-203``)
+-- ``wrapper(data)``, ``sync_gradients()``, ``cleanup()``, attribute passthrough, the same bucket
+rule -- with the machinery underneath replaced:
+
+===========================================  =================================================
+reference                                    here
+===========================================  =================================================
+tensor hook + spin on ``grad is None``       ``register_post_accumulate_grad_hook``
+sender thread: ``fuse`` (187 copies, D2H)    one ``dlb_pack`` launch per bucket on a side stream,
+                                             ordered after the bucket's last gradient by an event
+``reducer.put`` -> mp.Queue -> host sum      one allreduce kernel over NVLink peer memory
+-> gloo ring -> mp.Queue                     (``csrc/allreduce.cu``), variant chosen per size
+receiver thread: ``unfuse`` (187 copies)     ``.grad`` become views of the reduced buffer, or one
+                                             ``dlb_unpack`` launch
+``optimizer.step()`` (foreach SGD)           ``dlb_sgd_flat`` on the reduced buffer, or fused into
+                                             the allreduce kernel's epilogue
+``sync_gradients``: host waits on an Event   the compute stream waits on a CUDA event
+===========================================  =================================================
+
+At the first forward the wrapper probes the graph once to find parameters the loss never reaches
+(GoogLeNet's aux heads) and leaves them out, lays the buckets out in the
+peer-mapped arena (two regions per bucket, used alternately), and re-homes the parameters of each
+bucket into one flat fp32 buffer (plus a bf16 copy for bf16 models) so the SGD update is a single
+flat pass with no tensor table.
+
+All ranks launch buckets in bucket order: a bucket that fills early waits for its
+predecessors, so every rank issues the same sequence of communication kernels.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+import torch.nn as nn
+
+from ..ops import fused as F_ops
+from ..ops.comm import NativeComm, _round_up
+from ..utils.logging import Level, print_d
+from .buckets import Bucket, find_unused_parameters, fusion_grouping
+from .wrappers import _Wrapper
+
+_NORM_TYPES = (nn.modules.batchnorm._BatchNorm, nn.LayerNorm, nn.GroupNorm)
+_REGION_ALIGN = 4096
+
+
+class _NativeBucket:
+    """A fusion bucket placed in the arena: two regions, flat master/momentum/shadow."""
+
+    def __init__(self, bucket: Bucket, offsets: List[int], comm_dtype: torch.dtype):
+        self.b = bucket
+        self.id = bucket.bucket_id
+        self.tensors = bucket.tensors
+        self.numel = bucket.numel
+        self.comm_dtype = comm_dtype
+        self.region_offsets = offsets            # two byte offsets in the arena's data area
+        self.regions: List[torch.Tensor] = []    # two flat views (comm dtype)
+        self.cur = 0
+        self.plan = F_ops.PackPlan.for_tensors(self.tensors, bucket.offsets)
+        self.master: Optional[torch.Tensor] = None
+        self.momentum: Optional[torch.Tensor] = None
+        self.shadow: Optional[torch.Tensor] = None
+        self.ready = 0
+        self.launched = False
+        self.reduced: Optional[torch.Tensor] = None   # where this step's averaged gradient lives
+        self.algo = "twoshot"
+        self.nblocks = 16
+        self.sgd_done_in_kernel = False
+
+    @property
+    def nbytes(self) -> int:
+        return self.numel * self.regions[0].element_size()
+
+
+class B200Dist(_Wrapper):
+    handles_dtype = True      # the trainer must not wrap forward in autocast
+
+    def __init__(self, model, reducer=None, grouping_size: int = 25 * 1024 * 1024, grad_buff_device=None, *,
+                 overlap: bool = True, algo: str = "auto", fused_sgd: bool = True, comm_dtype: str = "auto",
+                 model_dtype: str = "fp32", cuda_graph: bool = False, group=None, comm: Optional[NativeComm] = None,
+                 exclude_unused: bool = True, unpack: str = "view", tune: bool = False):
+        super().__init__(model, reducer)
+        d = self.__dict__
+        d["grouping_size"] = int(grouping_size)
+        d["overlap"] = bool(overlap)
+        d["algo"] = algo
+        d["fused_sgd"] = bool(fused_sgd)
+        d["exclude_unused"] = exclude_unused
+        d["unpack_mode"] = unpack                      # "view" (zero copy) | "copy" (dlb_unpack into own tensors)
+        d["tune_at_start"] = tune
+        d["model_dtype"] = torch.bfloat16 if model_dtype in ("bf16", torch.bfloat16) else torch.float32
+        d["comm_dtype"] = {"auto": d["model_dtype"], "fp32": torch.float32, "bf16": torch.bfloat16}[comm_dtype] \
+            if isinstance(comm_dtype, str) else comm_dtype
+        d["device"] = next(model.parameters()).device
+        if d["device"].type != "cuda":
+            raise ValueError("B200Dist needs the model on a CUDA device")
+        d["group"] = group
+        d["comm"] = comm
+        d["owns_comm"] = comm is None
+        d["buckets"] = None
+        d["unused"] = []
+        d["comm_stream"] = torch.cuda.Stream(device=d["device"])
+        d["_hooks"] = []
+        d["_next"] = 0
+        d["_armed"] = False
+        d["_held"] = []
+        d["_last_event"] = None
+        d["optimizer"] = None
+        d["_fp32_stash"] = None
+        d["kernel_launches"] = 0
+        if d["model_dtype"] == torch.bfloat16:
+            self._convert_to_bf16()
+
+    # ------------------------------------------------------------------------------------------
+    # set-up
+    # ------------------------------------------------------------------------------------------
+    def _convert_to_bf16(self) -> None:
+        """bf16 compute with fp32 master weights: everything but the normalisation layers goes to
+        bf16; the fp32 originals are kept until the flat master buffers exist."""
+        stash = {}
+        for mod in self.model.modules():
+            if isinstance(mod, _NORM_TYPES):
+                continue
+            for name, p in mod.named_parameters(recurse=False):
+                if p.dtype == torch.float32:
+                    stash[p] = p.detach().clone()
+                    p.data = p.data.to(torch.bfloat16)
+        self.__dict__["_fp32_stash"] = stash
+
+    def parameters_were_reloaded(self) -> None:
+        """Called after a checkpoint was copied into the parameters in place."""
+        if self.buckets is None:
+            if self._fp32_stash is not None:
+                for p in list(self._fp32_stash):
+                    self._fp32_stash[p] = p.detach().float()
+            return
+        for nb in self.buckets:
+            if nb.shadow is None:
+                continue
+            for t, off in zip(nb.tensors, nb.b.offsets):
+                if t.dtype == torch.bfloat16:
+                    nb.master[off:off + t.numel()].copy_(t.detach().reshape(-1))
+
+    def _probe_unused(self, data) -> List[torch.Tensor]:
+        """One throw-away forward to find parameters the loss does not reach; RNG state and
+        module buffers (BatchNorm statistics) are restored so the real step is unaffected."""
+        params = [p for p in self.model.parameters() if p.requires_grad]
+        if not self.exclude_unused:
+            return []
+        cpu_rng = torch.get_rng_state()
+        cuda_rng = torch.cuda.get_rng_state(self.device)
+        saved = [(b, b.detach().clone()) for b in self.model.buffers()]
+        out = self.model(data)
+        if isinstance(out, (tuple, list)):
+            out = out[0]
+        unused = find_unused_parameters(out, params)
+        del out
+        with torch.no_grad():
+            for b, v in saved:
+                b.copy_(v)
+        torch.set_rng_state(cpu_rng)
+        torch.cuda.set_rng_state(cuda_rng, self.device)
+        return unused
+
+    def _build(self, data) -> None:
+        d = self.__dict__
+        d["unused"] = self._probe_unused(data)
+        dead = {id(p) for p in self.unused}
+        params = [p for p in self.model.parameters() if p.requires_grad and id(p) not in dead]
+        if self.unused:
+            print_d(f"B200Dist: {len(self.unused)} parameter tensors never receive a gradient and are left out", Level.INFO)
+        esize = torch.empty((), dtype=self.comm_dtype).element_size()
+        plain = [Bucket(i, ts, dtype=self.comm_dtype, aligned=True, allocate=False)
+                 for i, ts in enumerate(fusion_grouping(params, self.grouping_size))]
+        # arena layout: two regions per bucket
+        off, buckets = 0, []
+        for b in plain:
+            size = _round_up(b.numel * esize, _REGION_ALIGN)
+            buckets.append(_NativeBucket(b, [off, off + size], self.comm_dtype))
+            off += 2 * size
+        if self.comm is None:
+            d["comm"] = NativeComm(self.group, self.device)
+        if self.comm.mode is None:
+            self.comm.allocate(off)
+        elif self.comm.nbytes - self.comm.data_offset < off:
+            raise RuntimeError("the communicator's arena is too small for this model's buckets")
+        world = self.comm.world
+        for nb in buckets:
+            nb.regions = [self.comm.view(o, nb.numel, self.comm_dtype) for o in nb.region_offsets]
+            nb.b.grad_buffer = nb.regions[0]
+            if world > 1:
+                nb.algo, nb.nblocks = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
+            self._flatten_parameters(nb)
+        d["buckets"] = buckets
+        for nb in buckets:
+            for t in nb.tensors:
+                self._hooks.append(t.register_post_accumulate_grad_hook(self._make_hook(nb)))
+        d["_fp32_stash"] = None
+        if self.tune_at_start and world > 1:
+            sizes = sorted({nb.numel * esize for nb in buckets})
+            self.comm.tune(sizes, self.comm_dtype)
+            for nb in buckets:
+                nb.algo, nb.nblocks = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
+        print_d("B200Dist: " + ", ".join(f"bucket{nb.id}: {len(nb.tensors)} tensors {nb.numel * esize / 2**20:.2f} MiB "
+                                         f"{nb.algo}/{nb.nblocks}" for nb in buckets)
+                + f" (arena {self.comm.mode}, multicast {'yes' if self.comm.has_multicast else 'no'})", Level.INFO)
+
+    def _flatten_parameters(self, nb: _NativeBucket) -> None:
+        """Re-home the bucket's parameters in one flat fp32 buffer (and a bf16 copy for bf16
+        parameters).  fp32 parameters become views of the master buffer, bf16 parameters views
+        of the shadow buffer; values are unchanged."""
+        dev = self.device
+        nb.master = torch.zeros(nb.numel, dtype=torch.float32, device=dev)
+        nb.momentum = torch.zeros(nb.numel, dtype=torch.float32, device=dev)
+        need_shadow = any(t.dtype == torch.bfloat16 for t in nb.tensors)
+        nb.shadow = torch.zeros(nb.numel, dtype=torch.bfloat16, device=dev) if need_shadow else None
+        stash = self._fp32_stash or {}
+        with torch.no_grad():
+            for t, off in zip(nb.tensors, nb.b.offsets):
+                n = t.numel()
+                src = stash.get(t, t.detach())
+                nb.master[off:off + n].copy_(src.reshape(-1))
+                if t.dtype == torch.bfloat16:
+                    nb.shadow[off:off + n].copy_(nb.master[off:off + n])
+                    t.data = nb.shadow[off:off + n].view(t.shape)
+                else:
+                    t.data = nb.master[off:off + n].view(t.shape)
+
+    # ------------------------------------------------------------------------------------------
+    # the step
+    # ------------------------------------------------------------------------------------------
+    def _make_hook(self, nb: _NativeBucket):
+        def hook(_param):
+            if not self._armed:
+                return
+            nb.ready += 1
+            if nb.ready == len(nb.tensors) and self.overlap:
+                self._launch_ready()
+        return hook
+
+    def _launch_ready(self) -> None:
+        buckets = self.buckets
+        while self._next < len(buckets) and buckets[self._next].ready == len(buckets[self._next].tensors):
+            self._launch(buckets[self._next])
+            self.__dict__["_next"] = self._next + 1
+
+    def _launch(self, nb: _NativeBucket) -> None:
+        """Pack + allreduce (+ SGD) of one bucket on the communication stream."""
+        comm, world = self.comm, self.comm.world
+        cs = self.comm_stream
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(self.device))
+        cs.wait_event(ready)
+        grads = [t.grad for t in nb.tensors]
+        self._held.append(grads)              # keep the memory alive until the compute stream has waited for us
+        src, dst = nb.regions[nb.cur], nb.regions[1 - nb.cur]
+        opt = self.optimizer
+        in_kernel = self.fused_sgd and opt is not None and world > 1
+        nb.plan.pack(src, grads, 1.0 / world, stream=cs)
+        launches = 1
+        if world > 1:
+            sgd = None
+            if in_kernel:
+                sgd = F_ops.fused_sgd_args(nb.master, nb.momentum, opt.hyper(), nb.shadow)
+            if nb.algo == "oneshot":
+                comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, "oneshot", 1.0,
+                               out_offset=nb.region_offsets[1 - nb.cur], sgd=sgd, nblocks=nb.nblocks, stream=cs)
+                nb.reduced = dst
+            else:
+                comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, nb.algo, 1.0, sgd=sgd,
+                               nblocks=nb.nblocks, stream=cs)
+                nb.reduced = src
+            launches += 1
+        else:
+            nb.reduced = src
+        nb.sgd_done_in_kernel = in_kernel
+        nb.cur ^= 1
+        if self.unpack_mode == "copy":
+            fresh = [torch.empty_like(t) for t in nb.tensors]
+            with torch.cuda.stream(cs):
+                nb.plan.unpack(nb.reduced, fresh, 1.0, stream=cs)
+            launches += 1
+            views = fresh
+        else:
+            views = nb.b.grad_views(nb.reduced)
+        for t, v in zip(nb.tensors, views):
+            t.grad = v if v.dtype == t.dtype else None     # a view in another dtype cannot be a .grad
+        done = torch.cuda.Event()
+        done.record(cs)
+        nb.launched = True
+        self.__dict__["_last_event"] = done
+        self.__dict__["kernel_launches"] = self.kernel_launches + launches
+
+    def forward(self, data):
+        if self.model_dtype == torch.bfloat16 and data.is_floating_point() and data.dtype != torch.bfloat16:
+            data = data.to(torch.bfloat16)
+        if self.buckets is None:
+            self._build(data)
+        for nb in self.buckets:
+            nb.ready = 0
+            nb.launched = False
+        d = self.__dict__
+        d["_next"] = 0
+        d["_armed"] = True
+        d["_last_event"] = None
+        return self.model(data)
+
+    def sync_gradients(self) -> None:
+        if self.buckets is None:
+            return
+        if not self.overlap or self._next < len(self.buckets):
+            # fusion-only mode, or buckets that autograd never completed (should not happen)
+            for nb in self.buckets[self._next:]:
+                if nb.ready != len(nb.tensors):
+                    raise RuntimeError(f"bucket {nb.id}: {nb.ready}/{len(nb.tensors)} gradients arrived; "
+                                       "did the set of used parameters change?")
+                self._launch(nb)
+            self.__dict__["_next"] = len(self.buckets)
+        if self._last_event is not None:
+            torch.cuda.current_stream(self.device).wait_event(self._last_event)
+        self._held.clear()
+        self.__dict__["_armed"] = False
+
+    def make_optimizer(self, lr: float = 0.01, momentum: float = 0.5, **kw) -> "FusedSGD":
+        opt = FusedSGD(self, lr=lr, momentum=momentum, **kw)
+        self.__dict__["optimizer"] = opt
+        return opt
+
+    def cleanup(self) -> None:
+        for h in self._hooks:
+            h.remove()
+        self._hooks.clear()
+        torch.cuda.synchronize(self.device)
+        if self.comm is not None and self.comm.mode is not None:
+            self.comm.check()
+            if self.owns_comm:
+                self.comm.close()
+
+
+class FusedSGD:
+    """SGD-momentum over ``B200Dist``'s flat buffers (reference: ``optim.SGD(lr=0.01,
+    momentum=0.5)``, ``src/main.py:36``).  ``step`` launches one ``dlb_sgd_flat`` per bucket on the
+    current stream, reading the reduced gradient where the allreduce left it -- or nothing at all
+    for buckets whose update already ran inside the allreduce kernel.  ``state_dict`` has
+    ``torch.optim.SGD``'s layout, so checkpoints move between backends."""
+
+    def __init__(self, wrapper: B200Dist, lr: float = 0.01, momentum: float = 0.5, dampening: float = 0.0,
+                 weight_decay: float = 0.0, nesterov: bool = False):
+        self.wrapper = wrapper
+        self.param_groups = [dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay,
+                                  nesterov=nesterov, maximize=False, foreach=None, differentiable=False, fused=None)]
+        self._hyper_key = None
+        self._hyper = None
+        self._pending_state: Optional[dict] = None
+        self.steps = 0
+
+    def hyper(self):
+        g = self.param_groups[0]
+        key = (g["lr"], g["momentum"], g["dampening"], g["weight_decay"], g["nesterov"])
+        if key != self._hyper_key:
+            self._hyper = F_ops.make_hyper(*key[:4], nesterov=key[4])
+            self._hyper_key = key
+        return self._hyper
+
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        for p in self.wrapper.model.parameters():
+            if set_to_none:
+                p.grad = None
+            elif p.grad is not None:
+                p.grad.detach_().zero_()
+
+    def step(self) -> None:
+        w = self.wrapper
+        if w.buckets is None:
+            return
+        if self._pending_state is not None:
+            self._apply_state(self._pending_state)
+            self._pending_state = None
+        h = self.hyper()
+        for nb in w.buckets:
+            if nb.sgd_done_in_kernel:
+                nb.sgd_done_in_kernel = False
+                continue
+            if nb.reduced is None:
+                continue
+            F_ops.sgd_flat(nb.master, nb.momentum, nb.reduced, h, nb.shadow)
+            w.__dict__["kernel_launches"] = w.kernel_launches + 1
+        self.steps += 1
+
+    # -- torch.optim.SGD-compatible state ----------------------------------------------------------
+    def _param_index(self) -> Dict[int, int]:
+        return {id(p): i for i, p in enumerate(self.wrapper.model.parameters())}
+
+    def state_dict(self) -> dict:
+        w = self.wrapper
+        index = self._param_index()
+        state = {}
+        if w.buckets is not None and self.steps > 0:
+            for nb in w.buckets:
+                for t, off in zip(nb.tensors, nb.b.offsets):
+                    state[index[id(t)]] = {"momentum_buffer": nb.momentum[off:off + t.numel()].view(t.shape).clone()}
+        elif self._pending_state is not None:
+            state = self._pending_state["state"]
+        group = dict(self.param_groups[0])
+        group["params"] = list(range(len(index)))
+        return {"state": state, "param_groups": [group]}
+
+    def load_state_dict(self, sd: dict) -> None:
+        g = sd["param_groups"][0]
+        for k in ("lr", "momentum", "dampening", "weight_decay", "nesterov"):
+            if k in g:
+                self.param_groups[0][k] = g[k]
+        if self.wrapper.buckets is None:
+            self._pending_state = sd          # the flat buffers do not exist before the first forward
+        else:
+            self._apply_state(sd)
+
+    def _apply_state(self, sd: dict) -> None:
+        index = self._param_index()
+        for nb in self.wrapper.buckets:
+            for t, off in zip(nb.tensors, nb.b.offsets):
+                st = sd["state"].get(index[id(t)]) or sd["state"].get(str(index[id(t)]))
+                if st is not None and st.get("momentum_buffer") is not None:
+                    nb.momentum[off:off + t.numel()].copy_(st["momentum_buffer"].reshape(-1))
+                    self.steps = max(self.steps, 1)
