@@ -1,0 +1,144 @@
+"""The b200 arm of bench.py: B200Dist + FusedSGD on N GPUs, device-timed and end to end."""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+
+def _make_step(wrapper, opt):
+    def step(data, target):
+        opt.zero_grad()
+        out = wrapper(data)
+        loss = F.nll_loss(out.float() if out.dtype != torch.float32 else out, target)
+        loss.backward()
+        wrapper.sync_gradients()
+        opt.step()
+        return loss
+    return step
+
+
+def _timed(batches, k, device, clocks=None):
+    """Exactly k steps between two events, barrier + synchronize on both sides; returns ms."""
+    torch.cuda.synchronize(device)
+    if dist.is_initialized():
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    if clocks is not None:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(k):
+        batches(i)
+    e1.record()
+    torch.cuda.synchronize(device)
+    if dist.is_initialized():
+        dist.barrier()
+    stats = clocks.stop() if clocks is not None else None
+    return e0.elapsed_time(e1), stats
+
+
+def run(args, helpers) -> dict:
+    from distributed_learning_b200.models import create_network
+    from distributed_learning_b200.parallel.native import B200Dist
+    from distributed_learning_b200.trainer import broadcast_initial_state
+    from distributed_learning_b200.utils.data import INPUT_SPECS, PinnedPrefetcher
+
+    rank, local_rank, world = helpers.dist_env()
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE is {world}: launch N>1 with torch.distributed.run")
+    device = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(device)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world)
+
+    model_type = helpers.MODEL_ALIASES[args.model]
+    dtype = args.dtype or ("bf16" if model_type == "resnet50" else "fp32")
+    torch.manual_seed(1234)
+    model = create_network[model_type]().to(device)
+    if args.channels_last:
+        model = model.to(memory_format=torch.channels_last)
+    model.train()
+    broadcast_initial_state(model)          # before wrapping: the wrapper re-homes the parameters
+    wrapper = B200Dist(model, None, args.grouping_size, device, overlap=bool(args.overlap), algo=args.algo,
+                       fused_sgd=bool(args.fused_sgd), model_dtype=dtype, tune=bool(args.tune))
+    opt = wrapper.make_optimizer(lr=0.01, momentum=0.5)
+    step = _make_step(wrapper, opt)
+
+    shape, classes = INPUT_SPECS[model_type]
+    bs = args.batch_size
+    in_dtype = torch.bfloat16 if dtype == "bf16" else torch.float32
+    fmt = torch.channels_last if args.channels_last else torch.contiguous_format
+    # device-resident pool, larger than the 126 MB L2, rotated every step
+    in_bytes = bs * shape[0] * shape[1] * shape[2] * (2 if dtype == "bf16" else 4)
+    pool_n = max(2, -(-(160 << 20) // in_bytes))
+    pool_n = min(pool_n, 64)
+    g = torch.Generator(device=device).manual_seed(1000 + rank)
+    pool = [(torch.rand((bs,) + shape, device=device, generator=g).to(in_dtype).contiguous(memory_format=fmt),
+             torch.randint(classes, (bs,), device=device, generator=g)) for _ in range(pool_n)]
+
+    for i in range(args.warmup):
+        step(*pool[i % pool_n])
+    launches0 = wrapper.kernel_launches
+    ms, clocks = _timed(lambda i: step(*pool[i % pool_n]), args.steps, device, helpers.ClockSampler(local_rank))
+    launches = wrapper.kernel_launches - launches0
+    ms = helpers.max_over_ranks(ms)
+    images = bs * world * args.steps
+    value = images / (ms / 1000.0)
+
+    e2e = None
+    if not args.no_e2e:
+        # end to end through the public API: pinned host batches -> PinnedPrefetcher (H2D every
+        # step) -> wrapper/optimizer -> loss read back to the host every step
+        host_pool = [(torch.rand((bs,) + shape).contiguous(memory_format=fmt), torch.randint(classes, (bs,)))
+                     for _ in range(min(pool_n, 4))]
+
+        def host_batches():
+            i = 0
+            while True:
+                yield host_pool[i % len(host_pool)]
+                i += 1
+
+        pref = PinnedPrefetcher(host_batches(), device, depth=2, data_dtype=in_dtype,
+                                channels_last=bool(args.channels_last))
+        losses = []
+
+        def e2e_step(_i):
+            data, target = next(pref)
+            losses.append(step(data, target).item())
+
+        for i in range(2):
+            e2e_step(i)
+        ms2, _ = _timed(e2e_step, args.steps, device)
+        ms2 = helpers.max_over_ranks(ms2)
+        e2e = {"value": images / (ms2 / 1000.0), "unit": "images/s", "ms_per_step": ms2 / args.steps,
+               "h2d_bytes_per_step": pref.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
+               "last_loss": losses[-1] if losses else None}
+
+    wrapper.comm.check()
+    buckets = [{"mib": round(nb.numel * nb.regions[0].element_size() / 2**20, 2), "algo": nb.algo, "nblocks": nb.nblocks}
+               for nb in wrapper.buckets]
+    result = {
+        "metric": "training images/sec (GoogLeNet-class CNN, data parallel, device-timed, max over ranks)",
+        "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": (value / helpers.PUBLISHED_DDP[world]) if (model_type == "imagenet" and bs == 128 and world in helpers.PUBLISHED_DDP) else None,
+        "dtype": dtype, "data": "synthetic (random images of the named shape, random-init weights)",
+        "impl": "b200",
+        "config": {"model": {"imagenet": "googlenet(aux heads)", "resnet50": "resnet50", "mnist": "basicnet-mnist",
+                             "cifar": "basicnet-cifar"}[model_type],
+                   "global_batch": bs * world, "per_gpu_batch": bs, "seq_len": None,
+                   "input": list(shape), "parallelism": f"dp{world}", "optimizer": "sgd lr=0.01 momentum=0.5",
+                   "grouping_size": args.grouping_size, "buckets": buckets, "fused_sgd": bool(args.fused_sgd),
+                   "overlap": bool(args.overlap), "arena": wrapper.comm.mode, "multicast": wrapper.comm.has_multicast,
+                   "channels_last": bool(args.channels_last),
+                   "l2": f"inputs rotate over a {pool_n}-batch device pool ({pool_n * in_bytes >> 20} MiB > 126 MiB L2)"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+    }
+    wrapper.cleanup()
+    if world > 1:
+        dist.destroy_process_group()
+    return result

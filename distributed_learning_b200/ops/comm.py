@@ -96,8 +96,7 @@ class NativeComm:
 
     def _barrier(self):
         if self.world > 1:
-            self._dist.barrier(group=self.group) if self._dist.get_backend(self.group) != "nccl" else \
-                self._dist.barrier(group=self.group, device_ids=[self.device.index])
+            self._dist.barrier(group=self.group)
 
     def allocate(self, data_bytes: int) -> None:
         """Collective.  Allocates signal pad + ``data_bytes`` and maps all peers."""

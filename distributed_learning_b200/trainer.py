@@ -82,6 +82,11 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
     train_set = config.get_partition_dataset(node_id, worker_id, config.node_dev, config.total_dev,
                                              config.dataset_root, config.batch_size)
     model = prepare_model(config, device)
+    resuming = bool(getattr(config, "checkpoint", None) and getattr(config, "resume", 0)
+                    and os.path.exists(config.checkpoint))
+    if not resuming:
+        # before wrapping: the native wrapper re-homes the parameters in flat buffers
+        broadcast_initial_state(model, getattr(config, "worker_group", None))
     buff_device = device if gpu_reduce else "cpu"
     model = config.distribute_model(model, reducer, config.grouping_size, buff_device)
 
@@ -107,8 +112,6 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
         payload = load_checkpoint(ckpt, model, optimizer, map_location="cpu")
         batch_count, start_epoch = payload["batch_count"], payload["epoch"]
         print_d(f"Resumed from {ckpt} at batch {batch_count}", Level.INFO)
-    else:
-        broadcast_initial_state(model, getattr(config, "worker_group", None))
 
     timer = PhaseTimer(device, mode=getattr(config, "timer", "auto"))
     sync_loss = bool(getattr(config, "sync_loss", 0 if on_gpu else 1))

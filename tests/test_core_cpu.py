@@ -1,0 +1,219 @@
+"""CPU tests: models, CLI, timing CSV, data pipeline, checkpoint, library loading."""
+import os
+
+import pytest
+import torch
+
+from distributed_learning_b200.models import BasicNet, CifarNet, GoogLeNet, ResNet50, create_network
+from distributed_learning_b200.utils import timing
+from distributed_learning_b200.utils.config import parse_args, picklable_config
+from distributed_learning_b200.utils.data import (DataPartitioner, MNISTDataset, get_partition_dataset,
+                                                   random_data_generator, write_fake_image_folder, write_fake_mnist)
+from distributed_learning_b200.utils.logging import eval_arg
+
+ARGV = ["2", "1", "1", "2", "127.0.0.1", "lo", "mnist", "/tmp/x", "0"]
+
+
+# ---- models -----------------------------------------------------------------------------------
+def _shapes(m):
+    return [(n, tuple(p.shape)) for n, p in m.named_parameters()]
+
+
+def test_basicnet_matches_reference_shape():
+    m = BasicNet()
+    assert len(list(m.parameters())) == 8
+    assert sum(p.numel() for p in m.parameters()) == 1_199_882
+    assert m(torch.rand(2, 1, 28, 28)).shape == (2, 10)
+    c = CifarNet()
+    assert c.fc1.in_features == 64 * 14 * 14
+    out = c(torch.rand(3, 3, 32, 32))
+    assert out.shape == (3, 10) and torch.allclose(out.exp().sum(1), torch.ones(3), atol=1e-5)
+
+
+def test_googlenet_and_resnet_match_torchvision_parameter_layout():
+    tv = pytest.importorskip("torchvision.models")
+    with torch.device("meta"):
+        mine, theirs = GoogLeNet(), tv.googlenet(weights=None, init_weights=False)
+        assert [(n.replace("model.", "", 1), s) for n, s in _shapes(mine)] == _shapes(theirs)
+        assert sum(p.numel() for p in mine.parameters()) == 13_004_888
+        mine, theirs = ResNet50(), tv.resnet50(weights=None)
+        assert [(n.replace("model.", "", 1), s) for n, s in _shapes(mine)] == _shapes(theirs)
+        assert sum(p.numel() for p in mine.parameters()) == 25_557_032
+
+
+def test_googlenet_forward_equals_torchvision_with_same_weights():
+    tv = pytest.importorskip("torchvision.models")
+    torch.manual_seed(0)
+    theirs = tv.googlenet(weights=None, init_weights=False, num_classes=10).eval()
+    mine = GoogLeNet(num_classes=10).eval()
+    mine.model.load_state_dict(theirs.state_dict())
+    x = torch.rand(2, 3, 96, 96)
+    with torch.no_grad():
+        assert torch.allclose(mine(x), torch.log_softmax(theirs(x), 1), atol=1e-5)
+
+
+def test_registry():
+    assert set(create_network) >= {"mnist", "imagenet", "cifar", "resnet50"}
+
+
+# ---- CLI -----------------------------------------------------------------------------------------
+def test_cli_reference_defaults_and_positionals():
+    c = parse_args(ARGV)
+    assert (c.size, c.rank, c.node_dev, c.total_dev, c.master_addr, c.ifname) == (2, 1, 1, 2, "127.0.0.1", "lo")
+    assert (c.job_id, c.experiment, c.limit_batches, c.backend, c.batch_size, c.random_input) == \
+        ("job", "main_ourdist", 3, "gloo", 128, 0)
+    assert c.epoch_count == 100 and c.grouping_size == 25 * 1024 * 1024
+    assert c.devices == ["cpu"] and c.create_network is BasicNet
+    g = parse_args(["1", "0", "4", "4", "a", "i", "imagenet", "/r", "1", "--backend", "b200"])
+    assert g.devices == ["cuda:0", "cuda:1", "cuda:2", "cuda:3"]
+    import pickle
+    pickle.dumps(picklable_config(c))
+    pickle.dumps(c)                      # the whole config crosses `spawn` in the 2-step experiments
+
+
+def test_cli_envarg(monkeypatch):
+    monkeypatch.setenv("MY_SIZE", "4")
+    monkeypatch.setenv("MY_RANK", "3")
+    c = parse_args(["envarg://MY_SIZE", "envarg://MY_RANK", "1", "4"] + ARGV[4:])
+    assert (c.size, c.rank) == (4, 3)
+    assert eval_arg("plain") == "plain"
+    with pytest.raises(KeyError):
+        eval_arg("envarg://DOES_NOT_EXIST_XYZ")
+
+
+def test_cli_rejects_bad_values():
+    with pytest.raises(SystemExit):
+        parse_args(ARGV[:6] + ["nosuchmodel"] + ARGV[7:])
+    with pytest.raises(SystemExit):
+        parse_args(["2", "0", "2", "3"] + ARGV[4:])
+
+
+# ---- timing --------------------------------------------------------------------------------------
+def test_timing_csv_is_byte_compatible(tmp_path):
+    t = timing.PhaseTimer(mode="host")
+    for k in range(2):
+        t.start("batch")
+        for ph in ("get_data", "data2dev", "zero_grad", "forward", "backprop", "sync", "optimizer_step"):
+            t.start(ph)
+            t.end(ph)
+        t.end("batch")
+        t.end_step("ourdist", {"batch_count": k, "data_len": 32})
+    path = tmp_path / "t.csv"
+    t.writeout(str(path))
+    lines = path.read_text().splitlines()
+    assert lines[0] == ("experiment_name, get_data, data2dev, zero_grad, forward, backprop, sync, "
+                        "optimizer_step, batch, batch_count, data_len")
+    assert lines[1].startswith("ourdist, ") and lines[1].endswith(", 0, 32") and len(lines) == 3
+    assert len(lines[1].split(", ")) == 11
+
+
+def test_timing_module_level_api_and_means(tmp_path):
+    timing.set_default_timer(timing.PhaseTimer(mode="host"))
+    timing.start_timer("a")
+    timing.end_timer("a")
+    timing.start_timer("a")
+    timing.end_timer("a")
+    timing.end_timing_experiment("x", {"batch_count": 0})
+    means = timing.get_default_timer().phase_means()
+    assert means["a"] >= 0
+    timing.writeout_timer(str(tmp_path / "m.csv"))
+    assert (tmp_path / "m.csv").read_text().startswith("experiment_name, a, batch_count")
+    with pytest.raises(KeyError):
+        timing.end_timer("never_started")
+
+
+# ---- data ------------------------------------------------------------------------------------------
+def test_partitioner_disjoint_whole_batches():
+    torch.manual_seed(1234)
+    parts = DataPartitioner(list(range(1000)), total_dev=3, batch_size=32).partitions
+    assert all(len(p) == 320 for p in parts)
+    assert len(set(torch.cat(parts).tolist())) == 960
+    with pytest.raises(ValueError):
+        DataPartitioner(list(range(10)), 4, 8)
+
+
+def test_mnist_reader_and_loader(tmp_path):
+    root = write_fake_mnist(str(tmp_path), n=256)
+    ds = MNISTDataset(os.path.join(root, "mnist"))
+    img, label = ds[0]
+    assert img.shape == (1, 28, 28) and 0 <= label < 10 and len(ds) == 256
+    torch.manual_seed(1234)
+    loader = get_partition_dataset["mnist"](0, 1, 2, 2, root, 16, num_workers=0)
+    x, y = next(iter(loader))
+    assert x.shape == (16, 1, 28, 28) and y.dtype == torch.int64 and len(loader) == 8
+
+
+def test_image_folder_and_synthetic_fallback(tmp_path):
+    pytest.importorskip("torchvision")
+    root = write_fake_image_folder(str(tmp_path), n=16, classes=2, size=40)
+    x, y = next(iter(get_partition_dataset["imagenet"](0, 0, 1, 1, root, 4, num_workers=0)))
+    assert x.shape == (4, 3, 224, 224)
+    x, y = next(iter(get_partition_dataset["cifar"](0, 0, 1, 1, str(tmp_path / "none"), 8, num_workers=0)))
+    assert x.shape == (8, 3, 32, 32)
+
+
+def test_random_data_generator_shapes():
+    gen = random_data_generator((torch.zeros(4, 1, 28, 28), torch.tensor([0, 9, 3, 1])))
+    x, y = next(gen)
+    assert x.shape == (4, 1, 28, 28) and int(y.max()) <= 9 and 0 <= float(x.min()) and float(x.max()) < 1
+
+
+# ---- checkpoint ------------------------------------------------------------------------------------
+def test_checkpoint_roundtrip(tmp_path):
+    from distributed_learning_b200.utils.checkpoint import load_checkpoint, save_checkpoint
+
+    torch.manual_seed(0)
+    m = CifarNet()
+    opt = torch.optim.SGD(m.parameters(), lr=0.01, momentum=0.5)
+    m(torch.rand(2, 3, 32, 32)).sum().backward()
+    opt.step()
+    path = save_checkpoint(str(tmp_path / "c" / "ck.pt"), m, opt, batch_count=7, epoch=1, config=parse_args(ARGV))
+    m2 = CifarNet()
+    opt2 = torch.optim.SGD(m2.parameters(), lr=0.01, momentum=0.5)
+    payload = load_checkpoint(path, m2, opt2)
+    assert payload["batch_count"] == 7 and payload["epoch"] == 1 and payload["config"]["experiment"] == "main_ourdist"
+    for a, b in zip(m.parameters(), m2.parameters()):
+        assert torch.equal(a, b)
+    sa, sb = opt.state_dict()["state"], opt2.state_dict()["state"]
+    assert all(torch.equal(sa[k]["momentum_buffer"], sb[k]["momentum_buffer"]) for k in sa)
+
+
+# ---- native library (host-only parts work without a GPU) ---------------------------------------------
+def test_library_builds_loads_and_reports_errors():
+    from distributed_learning_b200.ops import _lib
+
+    L = _lib.lib()
+    assert L.dlb_version() >= 100
+    assert L.dlb_emulated_flags_bytes(4) == 4 * (_lib.DLB_SIGNAL_BYTES + 4 * _lib.DLB_STATE_WORDS)
+    rc = L.dlb_pack(None, 7, None, None, None, None, 0, 1.0, None)       # bad dtype -> DLB_E_ARG + message
+    assert rc == _lib.DLB_E_ARG and b"dtype" in L.dlb_last_error()
+    with pytest.raises(_lib.DlbError):
+        _lib.check(rc)
+
+
+def test_fd_passing_between_processes():
+    """SCM_RIGHTS plumbing used to share VMM handles: send a pipe's read end through a socket."""
+    import ctypes
+    import multiprocessing as mp
+
+    from distributed_learning_b200.ops import _lib
+
+    L = _lib.lib()
+    name = f"dlb200-test-{os.getpid()}".encode()
+    lfd = ctypes.c_int()
+    _lib.check(L.dlb_fd_listen(name, ctypes.byref(lfd)))
+
+    def child(name):
+        from distributed_learning_b200.ops import _lib as l2
+        r, w = os.pipe()
+        os.write(w, b"hello")
+        l2.check(l2.lib().dlb_fd_send(name, r, 42, 5000))
+
+    p = mp.get_context("fork").Process(target=child, args=(name,))
+    p.start()
+    fd, tag = ctypes.c_int(), ctypes.c_int()
+    _lib.check(L.dlb_fd_accept(lfd.value, ctypes.byref(fd), ctypes.byref(tag), 10000))
+    p.join()
+    assert tag.value == 42 and os.read(fd.value, 5) == b"hello"
+    L.dlb_fd_close(fd.value)
+    L.dlb_fd_close(lfd.value)
