@@ -93,8 +93,8 @@ def run(args, helpers) -> dict:
     if not args.no_e2e:
         # end to end through the public API: pinned host batches -> PinnedPrefetcher (H2D every
         # step) -> wrapper/optimizer -> loss read back to the host every step
-        host_pool = [(torch.rand((bs,) + shape).contiguous(memory_format=fmt), torch.randint(classes, (bs,)))
-                     for _ in range(min(pool_n, 4))]
+        host_pool = [(torch.rand((bs,) + shape).contiguous(memory_format=fmt).pin_memory(),
+                      torch.randint(classes, (bs,)).pin_memory()) for _ in range(min(pool_n, 4))]
 
         def host_batches():
             i = 0

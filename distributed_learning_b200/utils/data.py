@@ -213,59 +213,93 @@ def synthetic_batches(model_type: str, batch_size: int, device, dtype=torch.floa
 
 
 class PinnedPrefetcher:
-    """Host->device input pipeline: pinned staging buffers and a copy stream one step ahead.
+    """Host->device input pipeline: a staging thread, pinned buffers, and a copy stream that runs
+    one step ahead of the compute stream.
 
-    ``source`` yields ``(data, target)`` CPU tensors.  Each batch is copied into one of
-    ``depth`` pinned slots, then to the device on ``copy_stream``; ``__next__`` makes the
-    compute stream wait on the copy's event and immediately queues the next copy.  Bytes moved
-    per step are in ``h2d_bytes_per_step``.  On a CPU device it degrades to a pass-through.
+    ``source`` yields ``(data, target)`` CPU tensors.  A background thread pulls batches and
+    stages them in one of ``depth`` pinned slots (batches that already live in pinned memory,
+    e.g. from a ``DataLoader(pin_memory=True)``, are used where they are).  ``__next__`` makes
+    the compute stream wait on the previous copy's event, hands out that batch and immediately
+    issues the next host->device copy on ``copy_stream``, so the copy of step i+1 overlaps the
+    compute of step i.  Bytes moved per step are in ``h2d_bytes_per_step``.  On a CPU device it
+    degrades to a pass-through.
     """
 
-    def __init__(self, source, device, depth: int = 2, data_dtype: Optional[torch.dtype] = None,
+    def __init__(self, source, device, depth: int = 3, data_dtype: Optional[torch.dtype] = None,
                  channels_last: bool = False):
+        import queue
+        import threading
+
         self.source = iter(source)
         self.device = torch.device(device)
         self.cuda = self.device.type == "cuda"
-        self.depth = depth
+        self.depth = max(2, depth)
         self.data_dtype = data_dtype
         self.channels_last = channels_last
         self.h2d_bytes_per_step = 0
-        self._slots = []
-        self._slot = 0
         self._ready = None
+        self._stop = False
         if self.cuda:
             self.copy_stream = torch.cuda.Stream(device=self.device)
+            self._slots = [None] * self.depth
+            self._free = queue.Queue()
+            for i in range(self.depth):
+                self._free.put(i)
+            self._staged = queue.Queue(maxsize=self.depth)
+            self._thread = threading.Thread(target=self._stage_loop, daemon=True, name="dlb200-prefetch")
+            self._thread.start()
         self._queue_next()
 
+    # -- staging thread ------------------------------------------------------------------------
+    def _stage_loop(self):
+        try:
+            for data, target in self.source:
+                if self._stop:
+                    break
+                if data.is_pinned() and target.is_pinned():
+                    item = (data, target, None)
+                else:
+                    i = self._free.get()
+                    if self._slots[i] is None:
+                        fmt = torch.channels_last if (self.channels_last and data.dim() == 4) else torch.contiguous_format
+                        self._slots[i] = (torch.empty(data.shape, dtype=data.dtype).contiguous(memory_format=fmt).pin_memory(),
+                                          torch.empty_like(target).pin_memory(), torch.cuda.Event())
+                    hd, ht, free_ev = self._slots[i]
+                    free_ev.synchronize()          # the copy that last read this slot has finished
+                    hd.copy_(data)
+                    ht.copy_(target)
+                    item = (hd, ht, i)
+                self._staged.put(item)
+            self._staged.put(None)
+        except BaseException as e:  # noqa: BLE001 - re-raised in the consumer
+            self._staged.put(e)
+
+    # -- consumer side ---------------------------------------------------------------------------
     def _queue_next(self):
-        nx = next(self.source, None)
-        if nx is None:
+        if not self.cuda:
+            nx = next(self.source, None)
+            self._ready = None if nx is None else (nx[0], nx[1], None)
+            return
+        item = self._staged.get()
+        if item is None:
             self._ready = None
             return
-        data, target = nx
-        if not self.cuda:
-            self._ready = (data, target, None)
-            return
-        if len(self._slots) < self.depth:
-            fmt = torch.channels_last if (self.channels_last and data.dim() == 4) else torch.contiguous_format
-            self._slots.append((torch.empty(data.shape, dtype=data.dtype).contiguous(memory_format=fmt).pin_memory(),
-                                torch.empty_like(target).pin_memory(),
-                                torch.cuda.Event()))
-        hd, ht, free_ev = self._slots[self._slot]
-        self._slot = (self._slot + 1) % self.depth
-        free_ev.synchronize()          # the copy that last used this slot has finished
-        hd.copy_(data)
-        ht.copy_(target)
+        if isinstance(item, BaseException):
+            raise item
+        hd, ht, slot = item
         with torch.cuda.stream(self.copy_stream):
             dd = hd.to(self.device, non_blocking=True)
             dt = ht.to(self.device, non_blocking=True)
             if self.data_dtype is not None and dd.dtype != self.data_dtype:
                 dd = dd.to(self.data_dtype)
-            free_ev.record(self.copy_stream)
             done = torch.cuda.Event()
             done.record(self.copy_stream)
+            if slot is not None:
+                self._slots[slot][2].record(self.copy_stream)
+        if slot is not None:
+            self._free.put(slot)
         self.h2d_bytes_per_step = hd.numel() * hd.element_size() + ht.numel() * ht.element_size()
-        self._ready = (dd, dt, done)
+        self._ready = (dd, dt, done, (hd, ht))     # keep the host tensors alive until the copy is consumed
 
     def __iter__(self):
         return self
@@ -273,7 +307,7 @@ class PinnedPrefetcher:
     def __next__(self):
         if self._ready is None:
             raise StopIteration
-        data, target, done = self._ready
+        data, target, done = self._ready[:3]
         if done is not None:
             cur = torch.cuda.current_stream(self.device)
             cur.wait_event(done)
@@ -281,6 +315,9 @@ class PinnedPrefetcher:
             target.record_stream(cur)
         self._queue_next()
         return data, target
+
+    def close(self) -> None:
+        self._stop = True
 
 
 # ------------------------------------------------------------------------------------------
