@@ -54,6 +54,7 @@ def parse_args():
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--ref-experiment", default="main_ddp")
     p.add_argument("--ref-backend", default="nccl")
+    p.add_argument("--ref-use-gpu", type=int, default=1, help="0: run the reference arm on the CPU (dry run of the plumbing)")
     return p.parse_args()
 
 

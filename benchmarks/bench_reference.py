@@ -59,8 +59,14 @@ def run(args, helpers) -> dict:
     env = dict(os.environ)
     env["TORCH_HOME"] = os.path.join(root, "baseline", "hub_cache")
     env.pop("MASTER_PORT", None)        # the reference sets its own (29501)
+    # The reference does its own env:// rendezvous on that port.  Under torchrun the environment
+    # says "an agent already runs the store" (TORCHELASTIC_USE_AGENT_STORE), which would make rank 0
+    # connect to port 29501 as a client instead of serving it, and every rank would wait forever.
+    for k in [k for k in env if k.startswith(("TORCHELASTIC_", "TORCH_NCCL_ASYNC", "ROLE_", "GROUP_"))] + \
+            ["RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "OMP_NUM_THREADS"]:
+        env.pop(k, None)
     cmd = [sys.executable, main_py, str(world), str(rank), "1", str(world), "127.0.0.1", "lo", REF_MODEL[model_type],
-           data_root, "1", "--experiment", args.ref_experiment, "--backend", args.ref_backend, "--random_input", "1",
+           data_root, str(int(getattr(args, "ref_use_gpu", 1))), "--experiment", args.ref_experiment, "--backend", args.ref_backend, "--random_input", "1",
            "--limit_batches", str(total), "--batch_size", str(bs), "--job_id", "bench"]
     clocks = helpers.ClockSampler(local_rank).start()
     log = os.path.join(work, "ref.log")

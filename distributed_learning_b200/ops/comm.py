@@ -78,6 +78,7 @@ class NativeComm:
         self.data_offset = _round_up(DLB_SIGNAL_BYTES, _ALIGN)
         self.peer_ptrs: List[int] = []
         self.mc_ptr: Optional[int] = None
+        self.mc_note = ""          # why multicast is unavailable, for the log
         self.local: Optional[torch.Tensor] = None
         self.state = torch.zeros(DLB_STATE_WORDS, dtype=torch.int32, device=self.device)
         self._sig_array = None
@@ -195,7 +196,11 @@ class NativeComm:
             sup = False
         else:
             yes = c_int()
-            sup = L.dlb_mc_supported(dev, ctypes.byref(yes)) == 0 and bool(yes.value)
+            rc = L.dlb_mc_supported(dev, ctypes.byref(yes))
+            sup = rc == 0 and bool(yes.value)
+            if not sup:
+                self.mc_note = (f"device attribute MULTICAST_SUPPORTED is 0" if rc == 0
+                                else f"multicast query failed: {L.dlb_last_error().decode()}")
         if not all(self._gather(sup)):
             return
         mc = c_uint64()
@@ -217,16 +222,18 @@ class NativeComm:
                 check(L.dlb_vmm_import_fd(pfd.value, ctypes.byref(mc)))
                 L.dlb_fd_close(pfd.value)
             check(L.dlb_mc_add_device(mc.value, dev))
-        except (DlbError, RuntimeError):
+        except (DlbError, RuntimeError) as e:
             step_ok = False
+            self.mc_note = f"multicast create/add failed: {e}"
         if not all(self._gather(step_ok)):      # also the "all devices added" barrier
             return
         try:
             check(L.dlb_mc_bind(mc.value, 0, mem_handle, rounded))
             mp = c_void_p()
             check(L.dlb_mc_map(dev, mc.value, rounded, ctypes.byref(mp)))
-        except DlbError:
+        except DlbError as e:
             step_ok = False
+            self.mc_note = f"multicast bind/map failed: {e}"
         if all(self._gather(step_ok)):
             self.mc_ptr = mp.value
             self._handles["mc"] = (mc.value, mp.value, rounded)
