@@ -19,12 +19,10 @@ def _run_workers(nproc, what, free_port, timeout=600):
     return r.stdout
 
 
-def test_allreduce_two_gpus(free_port):
-    _run_workers(2, "comm", free_port)
-
-
-def test_training_two_gpus(free_port):
-    _run_workers(2, "train", free_port)
+def test_allreduce_and_training_two_gpus(free_port):
+    """One torchrun for both parts: on a fresh box most of the time is process start-up."""
+    out = _run_workers(2, "all", free_port)
+    assert "arena mode vmm" in out or "arena mode ipc" in out
 
 
 def test_all_gpus(free_port):
