@@ -492,3 +492,75 @@ extern "C" int dlb_allreduce_emulated(int algo, void* const* bufs, void* const* 
         k = dtype == DLB_F32 ? pick_oneshot<float, true>(nranks) : pick_oneshot<__nv_bfloat16, true>(nranks);
     return launch(k, dim3(nblocks, nranks), nthreads, (cudaStream_t)stream, a, true);
 }
+
+// ---- dlb_allreduce_emulated_static: the emulated allreduce for callers that cannot allocate ---------
+//
+// dlb_allreduce_emulated needs a scratch buffer for its barrier flags and epoch counters, and
+// expects the caller to bring one.  Some callers have no way to get device memory: a plug-in
+// running inside a process whose allocator it does not own (a serving runtime that reserved all
+// of HBM at start-up and hands none of it to extensions), a self-test that runs late in a job
+// when the device is full, or a C host that links this library but nothing that wraps cudaMalloc.
+// For them this variant keeps the scratch inside the library: a fixed array in device memory,
+// 35 072 bytes, that every GPU which loads the library holds until the process exits.
+//
+// What the caller has to know:
+//   * Limits.  The array is sized for DLB_MAX_RANKS (8) emulated ranks and DLB_MAX_BLOCKS (64)
+//     CTAs per rank; anything larger is refused with DLB_E_LIMIT, nothing is launched.
+//   * First call.  The first call on each device looks up the array's device address
+//     (cudaGetSymbolAddress, with that device current).  Make that first call before starting
+//     any stream capture on the device; later calls only enqueue work on `stream`.
+//   * Shared state.  There is one array per device, shared by every call and every thread, and it
+//     still holds whatever the previous call left there.  Each call therefore clears the part it
+//     uses (cudaMemsetAsync on `stream`, ordered before the kernel) so flags and epoch counters
+//     start from zero whatever rank count the previous call used.  Two calls whose work overlaps on
+//     the same GPU (different streams, or different host threads) would clear and bump each
+//     other's flags: that is a race, and the caller must serialise them.
+//   * No allocation.  No cudaMalloc / cudaFree / allocating library call is made, here or below.
+namespace {
+
+constexpr size_t kStaticFlagsBytes = (size_t)DLB_MAX_RANKS * (DLB_SIGNAL_BYTES + 4 * DLB_STATE_WORDS);
+static __device__ __align__(256) unsigned char g_static_flags[kStaticFlagsBytes];
+
+constexpr int kMaxDevices = 64;
+void* g_static_flags_ptr[kMaxDevices] = {};  // device address of g_static_flags, per device; host-side cache
+bool g_static_flags_ready[kMaxDevices] = {};
+
+// In host code `g_static_flags` names a host-side shadow of the symbol, not device memory: the
+// address a kernel can use has to be asked for, once per device, with that device current.
+int static_flags_for_current_device(void** out) {
+    int dev = -1;
+    DLB_CUDA(cudaGetDevice(&dev));
+    DLB_REQUIRE(dev >= 0 && dev < kMaxDevices, DLB_E_LIMIT, "dlb_allreduce_emulated_static: device ordinal %d beyond %d", dev, kMaxDevices - 1);
+    if (!g_static_flags_ready[dev]) {
+        void* p = nullptr;
+        DLB_CUDA(cudaGetSymbolAddress(&p, g_static_flags));
+        DLB_REQUIRE(p != nullptr, DLB_E_UNSUPPORTED, "dlb_allreduce_emulated_static: no device address for the scratch array");
+        g_static_flags_ptr[dev] = p;
+        g_static_flags_ready[dev] = true;
+    }
+    *out = g_static_flags_ptr[dev];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" size_t dlb_emulated_static_scratch_bytes(void) { return kStaticFlagsBytes; }
+
+extern "C" int dlb_allreduce_emulated_static(int algo, void* const* bufs, void* const* outs, int nranks, int64_t numel,
+                                             int dtype, float scale, int nblocks, int nthreads, void* stream) {
+    DLB_REQUIRE(bufs != nullptr, DLB_E_ARG, "dlb_allreduce_emulated_static: null bufs");
+    DLB_REQUIRE(algo == 0 || algo == 1, DLB_E_ARG, "dlb_allreduce_emulated_static: algo must be 0 (two-shot) or 1 (one-shot)");
+    DLB_REQUIRE(nranks >= 1 && nranks <= DLB_MAX_RANKS, DLB_E_LIMIT,
+                "dlb_allreduce_emulated_static: %d ranks, the built-in scratch holds at most %d", nranks, DLB_MAX_RANKS);
+    DLB_REQUIRE(nblocks >= 1 && nblocks <= DLB_MAX_BLOCKS, DLB_E_LIMIT,
+                "dlb_allreduce_emulated_static: %d CTAs per rank, the built-in scratch holds at most %d", nblocks, DLB_MAX_BLOCKS);
+    DLB_REQUIRE(algo == 0 || outs != nullptr, DLB_E_ARG, "dlb_allreduce_emulated_static: one-shot needs outs");
+    void* flags = nullptr;
+    int rc = static_flags_for_current_device(&flags);
+    if (rc) return rc;
+    const size_t used = dlb_emulated_flags_bytes(nranks);
+    DLB_REQUIRE(used <= kStaticFlagsBytes, DLB_E_LIMIT, "dlb_allreduce_emulated_static: scratch of %zu bytes exceeds the built-in %zu", used, kStaticFlagsBytes);
+    // the array keeps the last call's flags and epochs (possibly laid out for another rank count)
+    DLB_CUDA(cudaMemsetAsync(flags, 0, used, (cudaStream_t)stream));
+    return dlb_allreduce_emulated(algo, bufs, outs, nullptr, flags, nranks, numel, dtype, scale, nblocks, nthreads, stream);
+}

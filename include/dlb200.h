@@ -171,6 +171,21 @@ int dlb_allreduce_emulated(int algo, void* const* bufs, void* const* outs, const
                            int nranks, int64_t numel, int dtype, float scale, int nblocks, int nthreads, void* stream);
 size_t dlb_emulated_flags_bytes(int nranks);
 
+/* dlb_allreduce_emulated without the caller-provided scratch, for callers that cannot allocate
+ * device memory (a plug-in inside a process whose allocator it does not own, a self-test on a
+ * full device, a bare C host).  No counterpart in the reference: it has no native code and no
+ * notion of scratch memory.  The flags live in a fixed array inside the library
+ * (dlb_emulated_static_scratch_bytes() = 35 072 bytes, resident on every GPU that loads the
+ * library until the process exits), sized for DLB_MAX_RANKS ranks and DLB_MAX_BLOCKS CTAs per
+ * rank; larger requests return DLB_E_LIMIT and launch nothing.  The first call on a device looks
+ * up the array's device address, so make it before any stream capture on that device.  Every call
+ * clears the part of the array it uses on `stream` before the kernel.  All calls on a device share
+ * the one array: calls whose GPU work overlaps race, so serialise them.  Inputs and outputs are
+ * the caller's as before; nothing is allocated or freed.  No fused-SGD option. */
+int dlb_allreduce_emulated_static(int algo, void* const* bufs, void* const* outs, int nranks, int64_t numel,
+                                  int dtype, float scale, int nblocks, int nthreads, void* stream);
+size_t dlb_emulated_static_scratch_bytes(void);
+
 #ifdef __cplusplus
 }
 #endif
