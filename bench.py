@@ -50,7 +50,9 @@ def parse_args():
     p.add_argument("--fused-sgd", type=int, default=1)
     p.add_argument("--overlap", type=int, default=1)
     p.add_argument("--tune", type=int, default=1, help="measure the allreduce variants once and pick per bucket size")
-    p.add_argument("--channels-last", type=int, default=0)
+    p.add_argument("--channels-last", type=int, default=1, help="NHWC activations/weights (layout only; same arithmetic)")
+    p.add_argument("--cudnn-benchmark", type=int, default=1, help="let cuDNN time its algorithms at the first step")
+    p.add_argument("--cuda-graph", type=int, default=1, help="capture the whole training step in a CUDA graph")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--ref-experiment", default="main_ddp")
     p.add_argument("--ref-backend", default="nccl")

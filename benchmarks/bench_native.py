@@ -58,13 +58,15 @@ def run(args, helpers) -> dict:
     model_type = helpers.MODEL_ALIASES[args.model]
     dtype = args.dtype or ("bf16" if model_type == "resnet50" else "fp32")
     torch.manual_seed(1234)
+    torch.backends.cudnn.benchmark = bool(args.cudnn_benchmark)
     model = create_network[model_type]().to(device)
     if args.channels_last:
         model = model.to(memory_format=torch.channels_last)
     model.train()
     broadcast_initial_state(model)          # before wrapping: the wrapper re-homes the parameters
     wrapper = B200Dist(model, None, args.grouping_size, device, overlap=bool(args.overlap), algo=args.algo,
-                       fused_sgd=bool(args.fused_sgd), model_dtype=dtype, tune=bool(args.tune))
+                       fused_sgd=bool(args.fused_sgd), model_dtype=dtype, tune=bool(args.tune),
+                       cuda_graph=bool(args.cuda_graph))
     opt = wrapper.make_optimizer(lr=0.01, momentum=0.5)
     step = _make_step(wrapper, opt)
 
@@ -80,6 +82,10 @@ def run(args, helpers) -> dict:
     pool = [(torch.rand((bs,) + shape, device=device, generator=g).to(in_dtype).contiguous(memory_format=fmt),
              torch.randint(classes, (bs,), device=device, generator=g)) for _ in range(pool_n)]
 
+    if args.cuda_graph:
+        from distributed_learning_b200.parallel.graph_step import GraphedTrainStep
+
+        step = GraphedTrainStep(wrapper, opt, pool[0][0], pool[0][1])      # one replay = one whole step
     for i in range(args.warmup):
         step(*pool[i % pool_n])
     launches0 = wrapper.kernel_launches
@@ -134,7 +140,8 @@ def run(args, helpers) -> dict:
                    "input": list(shape), "parallelism": f"dp{world}", "optimizer": "sgd lr=0.01 momentum=0.5",
                    "grouping_size": args.grouping_size, "buckets": buckets, "fused_sgd": bool(args.fused_sgd),
                    "overlap": bool(args.overlap), "arena": wrapper.comm.mode, "multicast": wrapper.comm.has_multicast,
-                   "channels_last": bool(args.channels_last),
+                   "channels_last": bool(args.channels_last), "cudnn_benchmark": bool(args.cudnn_benchmark),
+                   "cuda_graph": bool(args.cuda_graph),
                    "l2": f"inputs rotate over a {pool_n}-batch device pool ({pool_n * in_bytes >> 20} MiB > 126 MiB L2)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
     }

@@ -14,7 +14,7 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kChunk = 8192;  // elements per CTA
-constexpr int kUnroll = 4;    // 16-byte groups in flight per thread
+constexpr int kUnroll = 8;    // 16-byte groups in flight per thread: a CTA issues all its loads up front
 
 struct TensorTable {
     void* tensor[DLB_MAX_TENSORS];

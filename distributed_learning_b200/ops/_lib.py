@@ -18,7 +18,7 @@ from . import build as _build
 
 DLB_MAX_RANKS = 8
 DLB_MAX_BLOCKS = 64
-DLB_MAX_TENSORS = 128
+DLB_MAX_TENSORS = 512
 DLB_SIGNAL_BYTES = 2 * DLB_MAX_BLOCKS * DLB_MAX_RANKS * 4
 DLB_STATE_WORDS = DLB_MAX_BLOCKS + 8
 

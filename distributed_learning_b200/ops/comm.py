@@ -285,12 +285,14 @@ class NativeComm:
 
     def allreduce(self, offset: int, numel: int, dtype: torch.dtype, algo: str = "twoshot", scale: float = 1.0,
                   out_offset: Optional[int] = None, sgd: Optional[FusedSgd] = None, nblocks: Optional[int] = None,
-                  stream=None) -> None:
+                  stream=None, end_barrier: bool = False) -> None:
         """Sum ``numel`` elements at ``offset`` over all ranks (times ``scale``) on ``stream``.
 
-        two-shot / nvls work in place; one-shot writes to ``out_offset`` (no trailing barrier:
-        the caller alternates input buffers between consecutive uses).  ``sgd`` fuses the
-        parameter update.  Every rank must make the same sequence of calls."""
+        two-shot / nvls work in place; one-shot writes to ``out_offset``.  By default one-shot has
+        no trailing barrier and the caller must alternate input buffers between consecutive uses;
+        ``end_barrier=True`` adds the barrier so the same input buffer can be refilled right away
+        (needed when a step is replayed from a CUDA graph).  ``sgd`` fuses the parameter update.
+        Every rank must make the same sequence of calls."""
         L = lib()
         esize = torch.empty((), dtype=dtype).element_size()
         nblocks = nblocks or default_nblocks(numel * esize, algo)
@@ -305,7 +307,7 @@ class NativeComm:
                 raise ValueError("one-shot needs out_offset (it cannot work in place)")
             out = self.peer_ptrs[self.rank] + self.data_offset + out_offset if out_offset is not None else None
             check(L.dlb_allreduce_oneshot(self._bufs(offset), out, self._sig_array, self.state.data_ptr(), self.rank,
-                                          self.world, numel, code, scale, nblocks, self.nthreads, 0, sgd_p, st))
+                                          self.world, numel, code, scale, nblocks, self.nthreads, int(end_barrier), sgd_p, st))
         elif algo == "nvls":
             if not self.has_multicast:
                 raise RuntimeError("nvls requested but no multicast mapping exists")

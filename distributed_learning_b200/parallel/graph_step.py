@@ -1,0 +1,68 @@
+"""Whole-step CUDA graph: zero_grad + forward + loss + backward + pack + allreduce + SGD as one
+replayable graph.
+
+The reference's step is ~600 Python-launched kernels plus host-side threads and queues; for the
+small CNN the host is the bottleneck.  On the native backend everything a step
+does is stream work -- the hooks fire at *capture* time and enqueue the pack and the allreduce on
+the side stream, which joins the capture through its events, and the cross-GPU barrier keeps its
+epoch counters in device memory -- so the entire step can be captured once and replayed with one
+launch.  Replays run no Python, no hooks and no allocator.
+
+Constraints (checked or documented): static shapes; the learning rate and momentum are baked
+into the captured kernels (re-capture after changing them); the wrapper must be built with
+``cuda_graph=True`` so every step uses the same arena regions and the one-shot variant keeps its
+trailing barrier; all ranks must replay the same number of times.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import torch
+import torch.nn.functional as F
+
+
+class GraphedTrainStep:
+    def __init__(self, wrapper, optimizer, example_data: torch.Tensor, example_target: torch.Tensor,
+                 loss_fn: Callable = F.nll_loss, warmup: int = 3):
+        if not getattr(wrapper, "static_regions", True):
+            raise ValueError("build the wrapper with cuda_graph=True before capturing its step")
+        self.wrapper, self.optimizer, self.loss_fn = wrapper, optimizer, loss_fn
+        self.data = example_data.clone()
+        self.target = example_target.clone()
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.loss: Optional[torch.Tensor] = None
+        self.launches_per_step = 0
+        dev = self.data.device
+        # eager warm-up on a side stream: builds the buckets, tunes, lets cuDNN pick algorithms
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._eager()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        before = getattr(wrapper, "kernel_launches", 0)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = self._eager()
+        self.launches_per_step = getattr(wrapper, "kernel_launches", 0) - before
+
+    def _eager(self) -> torch.Tensor:
+        self.optimizer.zero_grad()
+        out = self.wrapper(self.data)
+        loss = self.loss_fn(out.float() if out.dtype != torch.float32 else out, self.target)
+        loss.backward()
+        self.wrapper.sync_gradients()
+        self.optimizer.step()
+        return loss.detach()
+
+    def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        """Run one training step on ``(data, target)``; returns the (static) loss tensor."""
+        if data.data_ptr() != self.data.data_ptr():
+            self.data.copy_(data, non_blocking=True)
+        if target.data_ptr() != self.target.data_ptr():
+            self.target.copy_(target, non_blocking=True)
+        self.graph.replay()
+        if hasattr(self.wrapper, "kernel_launches"):
+            self.wrapper.__dict__["kernel_launches"] = self.wrapper.kernel_launches + self.launches_per_step
+        return self.loss

@@ -109,6 +109,7 @@ class B200Dist(_Wrapper):
         d["optimizer"] = None
         d["_fp32_stash"] = None
         d["kernel_launches"] = 0
+        d["static_regions"] = bool(cuda_graph)   # graph replay reuses the captured region every step
         if d["model_dtype"] == torch.bfloat16:
             self._convert_to_bf16()
 
@@ -265,7 +266,8 @@ class B200Dist(_Wrapper):
                 sgd = F_ops.fused_sgd_args(nb.master, nb.momentum, opt.hyper(), nb.shadow)
             if nb.algo == "oneshot":
                 comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, "oneshot", 1.0,
-                               out_offset=nb.region_offsets[1 - nb.cur], sgd=sgd, nblocks=nb.nblocks, stream=cs)
+                               out_offset=nb.region_offsets[1 - nb.cur], sgd=sgd, nblocks=nb.nblocks, stream=cs,
+                               end_barrier=self.static_regions)
                 nb.reduced = dst
             else:
                 comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, nb.algo, 1.0, sgd=sgd,
@@ -275,7 +277,8 @@ class B200Dist(_Wrapper):
         else:
             nb.reduced = src
         nb.sgd_done_in_kernel = in_kernel
-        nb.cur ^= 1
+        if not self.static_regions:
+            nb.cur ^= 1          # alternate regions: lets one-shot go without a trailing barrier
         if self.unpack_mode == "copy":
             fresh = [torch.empty_like(t) for t in nb.tensors]
             with torch.cuda.stream(cs):

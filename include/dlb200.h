@@ -31,7 +31,7 @@ extern "C" {
 
 #define DLB_MAX_RANKS 8     /* one NVSwitch domain */
 #define DLB_MAX_BLOCKS 64   /* CTAs of one communication kernel */
-#define DLB_MAX_TENSORS 128 /* tensors per multi-tensor launch (longer lists become several launches) */
+#define DLB_MAX_TENSORS 512 /* tensors per multi-tensor launch (11 KB of kernel parameters; longer lists become several launches) */
 #define DLB_SIGNAL_BYTES (2 * DLB_MAX_BLOCKS * DLB_MAX_RANKS * 4) /* size of one rank's signal pad */
 #define DLB_STATE_WORDS (DLB_MAX_BLOCKS + 8)                       /* local epoch counters + error word */
 

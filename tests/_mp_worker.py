@@ -68,8 +68,9 @@ def check_allreduce(comm, rank, world, dev):
             raise AssertionError(f"rank {rank}: fused sgd via {algo} diverged: {(p - ref_p).abs().max().item()}")
 
 
-def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overlap=True, algo="auto"):
+def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overlap=True, algo="auto", graph=False):
     from distributed_learning_b200.models import CifarNet
+    from distributed_learning_b200.parallel.graph_step import GraphedTrainStep
     from distributed_learning_b200.parallel.native import B200Dist
 
     torch.manual_seed(11)
@@ -79,17 +80,25 @@ def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overl
     for mdl in (ref, mine):
         mdl.dropout1.p = 0.0
         mdl.dropout2.p = 0.0
-    w = B200Dist(mine, None, 256 * 1024, dev, fused_sgd=fused, overlap=overlap, algo=algo, model_dtype=model_dtype)
+    w = B200Dist(mine, None, 256 * 1024, dev, fused_sgd=fused, overlap=overlap, algo=algo, model_dtype=model_dtype,
+                 cuda_graph=graph)
     opt = w.make_optimizer(lr=0.01, momentum=0.5)
     ref_opt = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.5)
     g = torch.Generator(device=dev).manual_seed(500 + rank)
-    for step in range(4):
-        x = torch.rand(8, 3, 32, 32, device=dev, generator=g)
-        y = torch.randint(10, (8,), device=dev, generator=g)
-        opt.zero_grad()
-        F.nll_loss(w(x).float(), y).backward()
-        w.sync_gradients()
-        opt.step()
+    batches = [(torch.rand(8, 3, 32, 32, device=dev, generator=g), torch.randint(10, (8,), device=dev, generator=g))
+               for _ in range(5)]
+    gstep = None
+    for i, (x, y) in enumerate(batches):
+        if graph:
+            if gstep is None:       # one eager warm-up step on batch 0, then capture; later batches are replays
+                gstep = GraphedTrainStep(w, opt, x, y, warmup=1)
+            else:
+                gstep(x, y)
+        else:
+            opt.zero_grad()
+            F.nll_loss(w(x).float(), y).backward()
+            w.sync_gradients()
+            opt.step()
         ref_opt.zero_grad()
         F.nll_loss(ref(x), y).backward()
         for p in ref.parameters():
@@ -101,7 +110,7 @@ def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overl
     for (n, p), q in zip(mine.named_parameters(), ref.parameters()):
         if not torch.allclose(p.float(), q, rtol=tol, atol=tol):
             raise AssertionError(f"rank {rank}: parameter {n} diverged ({(p.float() - q).abs().max().item()}) "
-                                 f"[{model_dtype} fused={fused} overlap={overlap} algo={algo}]")
+                                 f"[{model_dtype} fused={fused} overlap={overlap} algo={algo} graph={graph}]")
     # replicas bit-identical across ranks
     flat = torch.cat([p.detach().float().reshape(-1) for p in mine.parameters()])
     parts = [torch.empty_like(flat) for _ in range(world)]
@@ -131,14 +140,15 @@ def main():
                 print(f"arena mode {prefer} unavailable: {e}")
             continue
         if rank == 0:
-            print(f"arena mode {comm.mode}, multicast {comm.has_multicast}")
+            print(f"arena mode {comm.mode}, multicast {comm.has_multicast} {comm.mc_note}")
         check_allreduce(comm, rank, world, dev)
         comm.check()
         comm.close()
     os.environ.pop("DLB200_ARENA", None)
     if what in ("all", "train"):
         for kw in (dict(), dict(fused=False), dict(overlap=False), dict(algo="oneshot"), dict(algo="twoshot"),
-                   dict(model_dtype="bf16")):
+                   dict(model_dtype="bf16"), dict(graph=True), dict(graph=True, algo="oneshot"),
+                   dict(graph=True, algo="twoshot", fused=False)):
             check_training(rank, world, dev, None, **kw)
     dist.barrier()
     if rank == 0:

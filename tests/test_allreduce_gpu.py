@@ -166,3 +166,51 @@ def test_b200dist_single_gpu_matches_plain_training(fused_sgd, model_dtype):
     sd = opt.state_dict()
     assert len(sd["state"]) == len(list(mine.parameters()))
     wrapper.cleanup()
+
+
+@pytest.mark.parametrize("model_dtype", ["fp32", "bf16"])
+def test_graphed_train_step_matches_eager(model_dtype):
+    """The whole step captured in a CUDA graph gives the same parameters as eager stepping."""
+    import torch.nn.functional as F
+
+    from distributed_learning_b200.models import CifarNet
+    from distributed_learning_b200.parallel.graph_step import GraphedTrainStep
+    from distributed_learning_b200.parallel.native import B200Dist
+
+    dev = _dev()
+    xs = [torch.rand(16, 3, 32, 32, device=dev) for _ in range(6)]
+    ys = [torch.randint(10, (16,), device=dev) for _ in range(6)]
+
+    def run(graphed):
+        torch.manual_seed(7)
+        net = CifarNet().to(dev).train()
+        net.dropout1.p = net.dropout2.p = 0.0
+        w = B200Dist(net, None, 1 << 20, dev, model_dtype=model_dtype, cuda_graph=graphed)
+        opt = w.make_optimizer(lr=0.01, momentum=0.5)
+        losses = []
+        if graphed:
+            # the warm-up inside GraphedTrainStep trains on the example batch: replay the same schedule eagerly below
+            step = GraphedTrainStep(w, opt, xs[0], ys[0], warmup=2)
+            for x, y in zip(xs, ys):
+                losses.append(step(x, y).item())
+        else:
+            def eager(x, y):
+                opt.zero_grad()
+                loss = F.nll_loss(w(x).float(), y)
+                loss.backward()
+                w.sync_gradients()
+                opt.step()
+                return loss.item()
+            for _ in range(2):                  # the 2 warm-up steps on xs[0] (the capture pass itself executes nothing)
+                eager(xs[0], ys[0])
+            for x, y in zip(xs, ys):
+                losses.append(eager(x, y))
+        flat = torch.cat([p.detach().float().reshape(-1) for p in net.parameters()])
+        w.cleanup()
+        return losses, flat
+
+    l_g, p_g = run(True)
+    l_e, p_e = run(False)
+    tol = 2e-2 if model_dtype == "bf16" else 1e-5
+    assert l_g == pytest.approx(l_e, rel=tol, abs=tol)
+    assert torch.allclose(p_g, p_e, rtol=tol, atol=tol)

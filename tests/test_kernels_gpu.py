@@ -51,7 +51,7 @@ def test_pack_none_tensor_and_unaligned_views_and_many_tensors():
     torch.manual_seed(1)
     base = torch.randn(5000, device=dev)
     view = base[1:4098]                      # data pointer not 16-byte aligned
-    n_many = 300                             # more than one table (DLB_MAX_TENSORS = 128)
+    n_many = 700                             # more than one table (DLB_MAX_TENSORS = 512)
     many = [torch.randn(17 + i, device=dev) for i in range(n_many)]
     tensors = [view, None] + many
     sizes = [view.numel(), 40] + [t.numel() for t in many]
