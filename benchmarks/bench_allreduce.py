@@ -66,6 +66,8 @@ def main():
     comm = NativeComm(device=device)
     region = (args.max_bytes + 4095) // 4096 * 4096
     comm.allocate(2 * region)
+    if rank == 0:
+        print(f"arena {comm.mode}, multicast {comm.has_multicast} {comm.mc_note}", flush=True)
     blocks = [int(b) for b in args.blocks.split(",")]
     algos = ["oneshot", "twoshot"] + (["nvls"] if comm.has_multicast else [])
     rows = []

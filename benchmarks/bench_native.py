@@ -140,6 +140,7 @@ def run(args, helpers) -> dict:
                    "input": list(shape), "parallelism": f"dp{world}", "optimizer": "sgd lr=0.01 momentum=0.5",
                    "grouping_size": args.grouping_size, "buckets": buckets, "fused_sgd": bool(args.fused_sgd),
                    "overlap": bool(args.overlap), "arena": wrapper.comm.mode, "multicast": wrapper.comm.has_multicast,
+                   "multicast_note": wrapper.comm.mc_note,
                    "channels_last": bool(args.channels_last), "cudnn_benchmark": bool(args.cudnn_benchmark),
                    "cuda_graph": bool(args.cuda_graph),
                    "l2": f"inputs rotate over a {pool_n}-batch device pool ({pool_n * in_bytes >> 20} MiB > 126 MiB L2)"},

@@ -198,6 +198,18 @@ extern "C" int dlb_vmm_alloc(int dev, size_t bytes, uint64_t* handle, void** ptr
         rc = dlb_vmm_granularity(dev, 0, &gran);
         if (rc) return rc;
     }
+    {   // the multicast granularity can grow with the object size: ask again for this size
+        CUresult (*mcGran)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags) = nullptr;
+        if (driver_fn("cuMulticastGetGranularity", &mcGran) == 0) {
+            CUmulticastObjectProp mp;
+            memset(&mp, 0, sizeof(mp));
+            mp.numDevices = DLB_MAX_RANKS;
+            mp.size = (bytes + gran - 1) / gran * gran;
+            mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+            size_t mg = 0;
+            if (mcGran(&mg, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED) == CUDA_SUCCESS && mg > gran) gran = mg;
+        }
+    }
     const size_t size = (bytes + gran - 1) / gran * gran;
     CUmemAllocationProp prop = vmm_prop(dev);
     DRV_FN(create, "cuMemCreate", CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long);
@@ -271,8 +283,10 @@ extern "C" int dlb_mc_create(int ndev, size_t bytes, uint64_t* mc_handle, size_t
     mp.numDevices = (unsigned)ndev;
     mp.size = bytes;
     mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    // dlb_vmm_alloc already rounded the arena to the recommended granularity for its size; only
+    // the minimum is a hard requirement here, so an arena made by dlb_vmm_alloc is never re-rounded
     size_t g = 0;
-    DRV(mcGran(&g, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED));
+    DRV(mcGran(&g, &mp, CU_MULTICAST_GRANULARITY_MINIMUM));
     mp.size = (bytes + g - 1) / g * g;
     CUmemGenericAllocationHandle h = 0;
     DRV(mcCreate(&h, &mp));

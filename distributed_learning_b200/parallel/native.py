@@ -205,7 +205,8 @@ class B200Dist(_Wrapper):
                 nb.algo, nb.nblocks = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
         print_d("B200Dist: " + ", ".join(f"bucket{nb.id}: {len(nb.tensors)} tensors {nb.numel * esize / 2**20:.2f} MiB "
                                          f"{nb.algo}/{nb.nblocks}" for nb in buckets)
-                + f" (arena {self.comm.mode}, multicast {'yes' if self.comm.has_multicast else 'no'})", Level.INFO)
+                + f" (arena {self.comm.mode}, multicast {'yes' if self.comm.has_multicast else 'no'}"
+                + (f": {self.comm.mc_note}" if self.comm.mc_note else "") + ")", Level.INFO)
 
     def _flatten_parameters(self, nb: _NativeBucket) -> None:
         """Re-home the bucket's parameters in one flat fp32 buffer (and a bf16 copy for bf16

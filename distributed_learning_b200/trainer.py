@@ -123,6 +123,13 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
         return f"Worker {node_id}:{worker_id} loss for batch {k}: {value}\n"
 
     random_input = int(getattr(config, "random_input", 0))
+    channels_last = bool(getattr(config, "channels_last", 0)) and on_gpu
+    if getattr(config, "cudnn_benchmark", 0):
+        torch.backends.cudnn.benchmark = True
+    use_graph = bool(getattr(config, "cuda_graph", 0)) and bool(getattr(model, "static_regions", False))
+    graph_step = None
+    if use_graph:
+        from .parallel.graph_step import GraphedTrainStep
     every = int(getattr(config, "checkpoint_every", 0) or 0)
     limit = config.limit_batches
     epoch = start_epoch
@@ -151,29 +158,46 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
 
             timer.start("data2dev")
             data, target = data.to(device, non_blocking=True), target.to(device, non_blocking=True)
+            if channels_last and data.dim() == 4:
+                data = data.contiguous(memory_format=torch.channels_last)
             timer.end("data2dev")
 
-            timer.start("zero_grad")
-            optimizer.zero_grad()
-            timer.end("zero_grad")
+            if use_graph:
+                # the whole step is one CUDA graph: the CSV keeps its columns, `forward` holds the
+                # replay and the phases inside it cannot be told apart (they overlap anyway)
+                for ph in ("zero_grad",):
+                    timer.start(ph)
+                    timer.end(ph)
+                timer.start("forward")
+                if graph_step is None:
+                    graph_step = GraphedTrainStep(model, optimizer, data, target)
+                loss = graph_step(data, target).clone()
+                timer.end("forward")
+                for ph in ("backprop", "sync", "optimizer_step"):
+                    timer.start(ph)
+                    timer.end(ph)
+            else:
+                timer.start("zero_grad")
+                optimizer.zero_grad()
+                timer.end("zero_grad")
 
-            timer.start("forward")
-            with autocast:
-                output = model(data)
-                loss = F.nll_loss(output.float() if output.dtype != torch.float32 else output, target)
-            timer.end("forward")
+                timer.start("forward")
+                with autocast:
+                    output = model(data)
+                    loss = F.nll_loss(output.float() if output.dtype != torch.float32 else output, target)
+                timer.end("forward")
 
-            timer.start("backprop")
-            loss.backward()
-            timer.end("backprop")
+                timer.start("backprop")
+                loss.backward()
+                timer.end("backprop")
 
-            timer.start("sync")
-            model.sync_gradients()
-            timer.end("sync")
+                timer.start("sync")
+                model.sync_gradients()
+                timer.end("sync")
 
-            timer.start("optimizer_step")
-            optimizer.step()
-            timer.end("optimizer_step")
+                timer.start("optimizer_step")
+                optimizer.step()
+                timer.end("optimizer_step")
 
             if sync_loss:
                 value = loss.item()

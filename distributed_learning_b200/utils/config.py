@@ -67,7 +67,8 @@ def build_parser() -> argparse.ArgumentParser:
                    help="native allreduce variant (auto: chosen per message size from measured bus bandwidth)")
     p.add_argument("--fused_sgd", type=int, default=1, help="b200 backend: apply SGD inside/after the allreduce kernel on the flat buffers")
     p.add_argument("--cuda_graph", type=int, default=0, help="b200 backend: capture the whole step in a CUDA graph")
-    p.add_argument("--channels_last", type=int, default=0)
+    p.add_argument("--channels_last", type=int, default=0, help="NHWC weights and activations on the GPU")
+    p.add_argument("--cudnn_benchmark", type=int, default=0, help="let cuDNN time its algorithms at the first step")
     p.add_argument("--timer", type=str, default="auto", choices=("auto", "host", "device"))
     p.add_argument("--sync_loss", type=int, default=None,
                    help="read the loss back every batch like the reference (default: 1 on cpu, 0 on gpu where losses are flushed at the end)")
