@@ -50,8 +50,13 @@ def _group_backend(config, one_process_per_gpu: bool) -> str:
 def init_process(config) -> None:
     """Initialise the node-level process group (one rank per node)."""
     print_d(config, Level.DEBUG)
+    port = master_port(config)
+    if os.environ.get("TORCHELASTIC_USE_AGENT_STORE") and str(port) != os.environ.get("MASTER_PORT"):
+        # under torchrun the env:// rendezvous expects the agent's store on torchrun's port; on any
+        # other port rank 0 has to host the store itself, otherwise every rank waits for a server
+        os.environ.pop("TORCHELASTIC_USE_AGENT_STORE")
     os.environ["MASTER_ADDR"] = config.master_addr
-    os.environ["MASTER_PORT"] = str(master_port(config))
+    os.environ["MASTER_PORT"] = str(port)
     os.environ.setdefault("GLOO_SOCKET_IFNAME", config.ifname)
     backend = _group_backend(config, one_process_per_gpu=config.node_dev == 1)
     dist.init_process_group(backend, rank=config.rank, world_size=config.size,

@@ -1,14 +1,15 @@
 #!/usr/bin/env bash
 # The measurement suite behind BENCH_NOTES.md: correctness at N ranks, the flagship bench (both
 # arms), the allreduce sweep, ResNet-50 bf16, the small-CNN config and the fusion sweeps.
-#   scripts/gpu_suite.sh <N> [quick]
+#   [SKIP="step names"] scripts/gpu_suite.sh <N>
 # Everything lands in gpurun_out/suite_n<N>/ (one .out/.err per step).
 set -u
 N=${1:-2}; MODE=${2:-full}
 ROOT="$(cd "$(dirname "$0")/.." && pwd)"; cd "$ROOT"
 OUT=gpurun_out/suite_n$N; mkdir -p "$OUT"
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-step() { local name=$1; shift; local t0; t0=$(date +%s); "$@" > "$OUT/$name.out" 2> "$OUT/$name.err"; local rc=$?
+SKIP=" ${SKIP:-} "
+step() { local name=$1; shift; case "$SKIP" in *" $name "*) echo "[$name] skipped"; return;; esac; local t0; t0=$(date +%s); "$@" > "$OUT/$name.out" 2> "$OUT/$name.err"; local rc=$?
          echo "[$name] rc=$rc $(( $(date +%s) - t0 ))s"; tail -n 1 "$OUT/$name.out" | cut -c1-400; }
 M="python main.py 1 0 $N $N 127.0.0.1 lo"
 
@@ -24,7 +25,7 @@ step resnet50_ddp   timeout 400 $TR --master-port 29707 main.py envarg://WORLD_S
 step bench_mnist    timeout 300 $TR --master-port 29708 bench.py --model mnist --gpus "$N" --steps 200 --warmup 20
 step ref_mnist_ddp  timeout 300 $TR --master-port 29709 bench.py --impl reference --model mnist --gpus "$N" --steps 50 --warmup 10
 step ref_mnist_ourdist_nccl timeout 240 $TR --master-port 29710 bench.py --impl reference --model mnist --ref-experiment main_ourdist_nccl --gpus "$N" --steps 50 --warmup 10
-if [ "$MODE" = full ]; then
+if true; then
   step googlenet_ddp_nccl timeout 400 $TR --master-port 29711 main.py envarg://WORLD_SIZE envarg://RANK 1 "$N" 127.0.0.1 lo imagenet /tmp/none 1 \
                     --backend nccl --experiment main_ddp --random_input 1 --limit_batches 25 --batch_size 128 \
                     --channels_last 1 --cudnn_benchmark 1 --results_root "$OUT/results" --master_port 29752 --job_id googlenet_ddp
