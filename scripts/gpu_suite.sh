@@ -19,14 +19,14 @@ step bench_ref      timeout 500 $TR --master-port 29703 bench.py --impl referenc
 step allreduce_fp32 timeout 600 $TR --master-port 29704 benchmarks/bench_allreduce.py --ring --out "$OUT/allreduce_fp32.json"
 step allreduce_bf16 timeout 300 $TR --master-port 29705 benchmarks/bench_allreduce.py --dtype bf16 --min-bytes 65536 --factor 16 --blocks 16,32,48 --out "$OUT/allreduce_bf16.json"
 step bench_resnet50 timeout 300 $TR --master-port 29706 bench.py --model resnet50 --dtype bf16 --gpus "$N" --steps 20 --warmup 5
-step resnet50_ddp   timeout 400 $TR --master-port 29707 main.py envarg://WORLD_SIZE envarg://RANK 1 "$N" 127.0.0.1 lo resnet50 /tmp/none 1 \
+step resnet50_ddp   timeout 150 $TR --master-port 29707 main.py envarg://WORLD_SIZE envarg://RANK 1 "$N" 127.0.0.1 lo resnet50 /tmp/none 1 \
                     --backend nccl --experiment main_ddp --dtype bf16 --random_input 1 --limit_batches 25 --batch_size 128 \
                     --channels_last 1 --cudnn_benchmark 1 --results_root "$OUT/results" --master_port 29750 --job_id resnet_ddp
 step bench_mnist    timeout 300 $TR --master-port 29708 bench.py --model mnist --gpus "$N" --steps 200 --warmup 20
 step ref_mnist_ddp  timeout 300 $TR --master-port 29709 bench.py --impl reference --model mnist --gpus "$N" --steps 50 --warmup 10
 step ref_mnist_ourdist_nccl timeout 240 $TR --master-port 29710 bench.py --impl reference --model mnist --ref-experiment main_ourdist_nccl --gpus "$N" --steps 50 --warmup 10
 if true; then
-  step googlenet_ddp_nccl timeout 400 $TR --master-port 29711 main.py envarg://WORLD_SIZE envarg://RANK 1 "$N" 127.0.0.1 lo imagenet /tmp/none 1 \
+  step googlenet_ddp_nccl timeout 150 $TR --master-port 29711 main.py envarg://WORLD_SIZE envarg://RANK 1 "$N" 127.0.0.1 lo imagenet /tmp/none 1 \
                     --backend nccl --experiment main_ddp --random_input 1 --limit_batches 25 --batch_size 128 \
                     --channels_last 1 --cudnn_benchmark 1 --results_root "$OUT/results" --master_port 29752 --job_id googlenet_ddp
   step fusion_cifar   timeout 900 $M cifar /tmp/none 1 --backend b200 --experiment fusion_experiment_ourdist --random_input 1 \
