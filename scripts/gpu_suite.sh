@@ -32,7 +32,7 @@ if true; then
   step fusion_cifar   timeout 900 $M cifar /tmp/none 1 --backend b200 --experiment fusion_experiment_ourdist --random_input 1 \
                     --limit_batches 60 --batch_size 128 --results_root "$OUT/results" --master_port 29760 --job_id cifar
   step fusion_googlenet timeout 900 $M imagenet /tmp/none 1 --backend b200 --experiment fusion_experiment_ourdist --random_input 1 \
-                    --limit_batches 20 --batch_size 128 --channels_last 1 --cudnn_benchmark 1 --results_root "$OUT/results" --master_port 29770 --job_id googlenet
+                    --limit_batches 14 --batch_size 128 --channels_last 1 --cudnn_benchmark 1 --results_root "$OUT/results" --master_port 29770 --job_id googlenet
   step experiment1_b200 timeout 900 $M cifar /tmp/none 1 --backend b200 --experiment experiment1 --random_input 1 \
                     --limit_batches 60 --batch_size 128 --results_root "$OUT/results" --master_port 29780 --job_id exp1
 fi
