@@ -79,8 +79,12 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
     if on_gpu:
         torch.cuda.set_device(device)
 
+    # with synthetic input only one real batch is ever read (for its shape): do not fork loader
+    # workers for that -- forking a process that already runs CUDA and communication threads
+    # makes the children abort at exit
+    loader_workers = 0 if int(getattr(config, "random_input", 0)) else 2
     train_set = config.get_partition_dataset(node_id, worker_id, config.node_dev, config.total_dev,
-                                             config.dataset_root, config.batch_size)
+                                             config.dataset_root, config.batch_size, num_workers=loader_workers)
     model = prepare_model(config, device)
     resuming = bool(getattr(config, "checkpoint", None) and getattr(config, "resume", 0)
                     and os.path.exists(config.checkpoint))
