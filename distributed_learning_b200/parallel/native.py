@@ -198,6 +198,12 @@ class B200Dist(_Wrapper):
             for t in nb.tensors:
                 self._hooks.append(t.register_post_accumulate_grad_hook(self._make_hook(nb)))
         d["_fp32_stash"] = None
+        opt = self.optimizer
+        if opt is not None and opt._pending_state is not None:
+            # a checkpoint was loaded before the flat buffers existed; the momentum has to be in
+            # place before the first bucket is launched, because the update runs inside that kernel
+            opt._apply_state(opt._pending_state)
+            opt._pending_state = None
         if self.tune_at_start and world > 1:
             sizes = sorted({nb.numel * esize for nb in buckets})
             self.comm.tune(sizes, self.comm_dtype)

@@ -353,3 +353,30 @@ def write_fake_image_folder(root: str, n: int = 256, classes: int = 4, size: int
         arr = rng.randint(0, 256, size=(size, size, 3), dtype=np.uint8)
         Image.fromarray(arr).save(os.path.join(d, f"img{i:05d}.jpg"), quality=60)
     return root
+
+
+# ------------------------------------------------------------------------------------------
+# legacy API: all of this node's partitions at once
+# ------------------------------------------------------------------------------------------
+def _partition_helper(node_dev: int, total_dev: int, dataset, batch_size: int = PER_WORKER_BATCH_SIZE, node_id=None):
+    """Loaders for every device of this node (reference ``_partition_helper``, ``src/data.py:44-56``;
+    unused by the reference's own experiments).  The node index comes from ``dist.get_rank()``
+    unless ``node_id`` is given."""
+    if node_id is None:
+        import torch.distributed as dist
+
+        node_id = dist.get_rank()
+    partitioner = DataPartitioner(dataset, total_dev, batch_size)
+    loaders = [DataLoader(partitioner.use(node_id * node_dev + i), batch_size=int(batch_size), shuffle=True)
+               for i in range(node_dev)]
+    return loaders, batch_size
+
+
+def partition_mnist(node_dev: int, total_dev: int, dataset_root: str, batch_size: int = PER_WORKER_BATCH_SIZE, node_id=None):
+    """Reference ``partition_mnist`` (``src/data.py:71-82``)."""
+    return _partition_helper(node_dev, total_dev, _dataset_for("mnist", dataset_root, total_dev, batch_size), batch_size, node_id)
+
+
+def partition_image_folder(node_dev: int, total_dev: int, dataset_root: str, batch_size: int = PER_WORKER_BATCH_SIZE, node_id=None):
+    """Reference ``partition_image_folder`` (``src/data.py:97-111``)."""
+    return _partition_helper(node_dev, total_dev, _dataset_for("imagenet", dataset_root, total_dev, batch_size), batch_size, node_id)

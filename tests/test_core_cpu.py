@@ -217,3 +217,44 @@ def test_fd_passing_between_processes():
     assert tag.value == 42 and os.read(fd.value, 5) == b"hello"
     L.dlb_fd_close(fd.value)
     L.dlb_fd_close(lfd.value)
+
+
+def test_legacy_partition_api(tmp_path):
+    from distributed_learning_b200.utils.data import partition_mnist
+
+    root = write_fake_mnist(str(tmp_path), n=512)
+    torch.manual_seed(1234)
+    loaders, bs = partition_mnist(2, 4, root, 16, node_id=1)
+    assert len(loaders) == 2 and bs == 16 and next(iter(loaders[1]))[0].shape == (16, 1, 28, 28)
+
+
+def test_summarize_results(tmp_path):
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "benchmarks"))
+    from summarize_results import summarise_folder
+
+    head = "experiment_name, get_data, data2dev, zero_grad, forward, backprop, sync, optimizer_step, batch, batch_count, data_len\n"
+    for w, batch in ((0, 10.0), (1, 20.0)):
+        with open(tmp_path / f"ourdist_0_{w}_times.csv", "w") as f:
+            f.write(head)
+            for k in range(8):
+                f.write(f"ourdist, 1.0, 0.1, 0.1, 3.0, 4.0, {w + 1.0}, 0.5, {batch if k >= 5 else 999.0}, {k}, 128\n")
+    s = summarise_folder(str(tmp_path), skip=5)["ourdist"]
+    assert s["workers"] == 2 and s["batch_ms"] == 20.0                  # mean over batches >= 5, max over workers
+    assert s["images_per_sec"] == pytest.approx(2 * 128 / 20.0 * 1000.0)
+    assert s["phases_ms"]["sync"] == 2.0
+
+
+def test_launcher_port_and_backend_selection(monkeypatch):
+    from distributed_learning_b200 import launcher
+
+    c = parse_args(ARGV + ["--master_port", "31234"])
+    assert launcher.master_port(c) == 31234
+    monkeypatch.setenv("MASTER_PORT", "30000")
+    assert launcher.master_port(parse_args(ARGV)) == 30000
+    monkeypatch.delenv("MASTER_PORT")
+    assert launcher.master_port(parse_args(ARGV)) == 29501              # the reference's fixed port
+    g = parse_args(["1", "0", "1", "1", "a", "i", "mnist", "/r", "1", "--backend", "b200"])
+    assert launcher._group_backend(g, one_process_per_gpu=True) == "cpu:gloo,cuda:nccl"
+    assert launcher._group_backend(g, one_process_per_gpu=False) == "gloo"
+    assert launcher._group_backend(parse_args(ARGV), True) == "gloo"
