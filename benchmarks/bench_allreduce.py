@@ -27,15 +27,32 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def timed(fn, warmup, iters, device):
+def timed(fn, warmup, iters, device, graph=False):
+    """ms per call of ``fn``: ``iters`` back-to-back launches between two events, max over ranks.
+    ``graph=True`` captures the ``iters`` launches in one CUDA graph first, which removes the host's
+    per-launch cost (Python + driver) and leaves the device-side time."""
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize(device)
+    replay = None
+    if graph:
+        side = torch.cuda.Stream(device=device)
+        side.wait_stream(torch.cuda.current_stream(device))
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            for _ in range(iters):
+                fn()
+        replay = g.replay
+        replay()
+        torch.cuda.synchronize(device)
     dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(iters):
-        fn()
+    if replay is not None:
+        replay()
+    else:
+        for _ in range(iters):
+            fn()
     e1.record()
     torch.cuda.synchronize(device)
     t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64)
@@ -51,6 +68,7 @@ def main():
     ap.add_argument("--dtype", default="fp32", choices=("fp32", "bf16"))
     ap.add_argument("--blocks", default="8,16,32,48,64")
     ap.add_argument("--ring", action="store_true", help="also time the reference-style host-driven NCCL send/recv ring")
+    ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays of the launches (device-side time, no host launch cost)")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
 
@@ -89,11 +107,12 @@ def main():
                 def run(algo=algo, nb=nb):
                     a, b = (0, region) if flip[0] == 0 else (region, 0)
                     flip[0] ^= 1
-                    comm.allreduce(a, numel, dtype, algo, scale=1.0 / world, out_offset=b, nblocks=nb)
+                    comm.allreduce(a, numel, dtype, algo, scale=1.0 / world, out_offset=b, nblocks=nb,
+                                   stream=torch.cuda.current_stream(device))
 
-                row["ms"][f"{algo}/{nb}"] = timed(run, 5, iters, device)
+                row["ms"][f"{algo}/{nb}"] = timed(run, 5, iters, device, args.graph)
         x = torch.randn(numel, device=device).to(dtype)
-        row["ms"]["nccl"] = timed(lambda: dist.all_reduce(x), 5, iters, device)
+        row["ms"]["nccl"] = timed(lambda: dist.all_reduce(x), 5, iters, device, args.graph)
         if args.ring and size >= 4096:
             row["ms"]["nccl_ring_hostdriven"] = timed(lambda: ring_allreduce_gpu(x), 2, max(2, iters // 10), device)
         native = {k: v for k, v in row["ms"].items() if not k.startswith("nccl")}
@@ -114,7 +133,8 @@ def main():
         size *= args.factor
     comm.check()
     result = {"n_gpus": world, "dtype": args.dtype, "arena": comm.mode, "multicast": comm.has_multicast,
-              "timing": "CUDA events, back-to-back launches, max over ranks", "rows": rows}
+              "timing": ("CUDA events around one CUDA-graph replay of the launches" if args.graph else
+                         "CUDA events, back-to-back launches") + ", max over ranks", "rows": rows}
     if rank == 0 and args.out:
         os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
         with open(args.out, "w") as f:

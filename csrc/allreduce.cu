@@ -63,7 +63,8 @@ __device__ __forceinline__ void block_barrier(const CommArgs& a, int rank, uint3
     __syncthreads();
     if ((int)threadIdx.x < ranks_of<NR>(a)) {
         const int peer = threadIdx.x;
-        __threadfence_system();  // the CTA's earlier (peer) writes become visible before the flag
+        // st.release.sys orders the whole CTA's earlier (peer) writes -- made visible to this thread
+        // by the __syncthreads above -- before the flag; no separate system fence is needed
         st_flag_release_sys(a.sig[peer] + blockIdx.x * DLB_MAX_RANKS + rank, epoch);
         const uint32_t* mine = a.sig[rank] + blockIdx.x * DLB_MAX_RANKS + peer;
         uint64_t t0 = 0;
