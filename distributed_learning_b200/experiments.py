@@ -227,8 +227,8 @@ def main_overlap(config):
 def main_ddp(config):
     config.experiment_name = "ddp"
     config.make_reducer = None
-    if config.backend == "b200":
-        raise SystemExit("main_ddp is the library baseline: run it with --backend nccl (or gloo)")
+    # on the native backend main_ddp stays what it is in the reference's suites: the library
+    # baseline.  The worker-level group carries NCCL for CUDA tensors, so torch DDP runs as is.
     if _device_backend(config):
         config.distribute_model = _ddp_cuda
         _run_device(config)

@@ -214,3 +214,32 @@ def test_graphed_train_step_matches_eager(model_dtype):
     tol = 2e-2 if model_dtype == "bf16" else 1e-5
     assert l_g == pytest.approx(l_e, rel=tol, abs=tol)
     assert torch.allclose(p_g, p_e, rtol=tol, atol=tol)
+
+
+def test_b200dist_unpack_copy_mode_gives_own_gradient_tensors():
+    """``unpack="copy"`` runs the dlb_unpack kernel: gradients land in fresh tensors, not arena views."""
+    import torch.nn.functional as F
+
+    from distributed_learning_b200.models import CifarNet
+    from distributed_learning_b200.parallel.native import B200Dist
+
+    dev = _dev()
+    torch.manual_seed(3)
+    ref = CifarNet().to(dev).train()
+    mine = CifarNet().to(dev).train()
+    mine.load_state_dict(ref.state_dict())
+    for m in (ref, mine):
+        m.dropout1.p = m.dropout2.p = 0.0
+    w = B200Dist(mine, None, 64 * 1024, dev, fused_sgd=False, unpack="copy")
+    opt = w.make_optimizer(lr=0.0)                       # lr 0: only look at the gradients
+    x, y = torch.rand(8, 3, 32, 32, device=dev), torch.randint(10, (8,), device=dev)
+    opt.zero_grad()
+    F.nll_loss(w(x), y).backward()
+    w.sync_gradients()
+    F.nll_loss(ref(x), y).backward()
+    torch.cuda.synchronize()
+    lo, hi = w.comm.local.data_ptr(), w.comm.local.data_ptr() + w.comm.nbytes
+    for p, q in zip(mine.parameters(), ref.parameters()):
+        assert torch.allclose(p.grad, q.grad, rtol=1e-5, atol=1e-6)
+        assert not (lo <= p.grad.data_ptr() < hi)
+    w.cleanup()

@@ -29,6 +29,12 @@ def test_main_native_backend_single_gpu(tmp_path, free_port, graph):
                  "--results_root", str(results), "--master_port", str(free_port()), "--cuda_graph", str(graph)])
     assert "topology:" in out and "NVIDIA" in out          # bring-up discovers the GPUs instead of a NIC
     folder = results / "experiment1_1_job"
+    if graph == 0:      # the 1-step suite too: its main_ddp runs torch DDP over NCCL inside the same group
+        _main(["1", "0", "1", "1", "127.0.0.1", "lo", "cifar", str(tmp_path / "data"), "1", "--backend", "b200",
+               "--experiment", "experiment2", "--random_input", "1", "--limit_batches", "4", "--batch_size", "32",
+               "--results_root", str(results), "--master_port", str(free_port())])
+        for name in ("ddp", "onestep_reduce", "onestep_central"):
+            assert len((results / "experiment2_1_job" / f"{name}_0_0_times.csv").read_text().splitlines()) == 5, name
     for name in ("warmup", "ourdist", "seq_merge", "overlap", "central_node_reduce"):
         rows = (folder / f"{name}_0_0_times.csv").read_text().splitlines()
         assert rows[0] == HEADER and len(rows) == 9, name

@@ -130,3 +130,33 @@ def test_sgd_multi_matches_torch_sgd():
     torch.cuda.synchronize()
     for p, r in zip(ps, ref):
         assert torch.allclose(p, r.detach(), rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("kw", [dict(lr=0.01, momentum=0.5), dict(lr=0.05, momentum=0.9, dampening=0.1, weight_decay=1e-3),
+                                dict(lr=0.02, momentum=0.9, nesterov=True), dict(lr=0.1)])
+def test_multi_tensor_sgd_optimizer_matches_torch(kw):
+    """The drop-in optimizer on a real model: same parameters and same state_dict as torch.optim.SGD."""
+    import torch.nn.functional as F
+
+    from distributed_learning_b200.models import CifarNet
+    from distributed_learning_b200.ops.optim import MultiTensorSGD
+
+    dev = _dev()
+    torch.manual_seed(9)
+    a, b = CifarNet().to(dev), CifarNet().to(dev)
+    b.load_state_dict(a.state_dict())
+    for m in (a, b):
+        m.dropout1.p = m.dropout2.p = 0.0
+    oa, ob = MultiTensorSGD(a.parameters(), **kw), torch.optim.SGD(b.parameters(), **kw)
+    for step in range(4):
+        x, y = torch.rand(8, 3, 32, 32, device=dev), torch.randint(10, (8,), device=dev)
+        for m, o in ((a, oa), (b, ob)):
+            o.zero_grad()
+            F.nll_loss(m(x), y).backward()
+            o.step()
+    for p, q in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(p, q, rtol=1e-5, atol=1e-6)
+    if kw.get("momentum"):
+        sa, sb = oa.state_dict()["state"], ob.state_dict()["state"]
+        assert all(torch.allclose(sa[k]["momentum_buffer"], sb[k]["momentum_buffer"], rtol=1e-5, atol=1e-6) for k in sb)
+        ob.load_state_dict(oa.state_dict())          # layouts are interchangeable
