@@ -210,6 +210,9 @@ def main_ourdist_nccl(config):
 
 @experiment
 def main_seq(config):
+    if config.backend == "b200":     # SeqDist = one reduction per parameter, after backward
+        _with_grouping(config, 0, lambda: _run(config, "seq", SeqDist, "ring", two_step=True, overlap=False))
+        return
     _run(config, "seq", SeqDist, "ring", two_step=True, overlap=False)
 
 

@@ -96,6 +96,10 @@ def finalize_config(config: argparse.Namespace) -> argparse.Namespace:
         config.devices = ["cpu"] * config.node_dev
     if config.sync_loss is None:
         config.sync_loss = 0 if config.use_gpu == 1 else 1
+    if config.backend == "b200" and config.use_gpu != 1:
+        raise SystemExit("--backend b200 is the NVLink path: it needs g=1 (use --backend gloo on the CPU)")
+    if config.backend == "b200" and config.total_dev > 8:
+        raise SystemExit("--backend b200 spans one NVSwitch domain (at most 8 GPUs); use --backend nccl beyond that")
     if config.size * config.node_dev != config.total_dev:
         # the reference does not check this and then mis-partitions the data silently
         raise SystemExit(f"n*d must equal D (got {config.size}*{config.node_dev} != {config.total_dev})")

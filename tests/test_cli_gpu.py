@@ -35,6 +35,11 @@ def test_main_native_backend_single_gpu(tmp_path, free_port, graph):
                "--results_root", str(results), "--master_port", str(free_port())])
         for name in ("ddp", "onestep_reduce", "onestep_central"):
             assert len((results / "experiment2_1_job" / f"{name}_0_0_times.csv").read_text().splitlines()) == 5, name
+        out = _main(["1", "0", "1", "1", "127.0.0.1", "lo", "cifar", str(tmp_path / "data"), "1", "--backend", "b200",
+                     "--experiment", "main_seq", "--random_input", "1", "--limit_batches", "3", "--batch_size", "32",
+                     "--results_root", str(results), "--master_port", str(free_port())])
+        assert "bucket7: 1 tensors" in out          # SeqDist on b200 = one bucket per parameter tensor
+        assert (results / "main_seq_1_job" / "seq_0_0_times.csv").exists()
     for name in ("warmup", "ourdist", "seq_merge", "overlap", "central_node_reduce"):
         rows = (folder / f"{name}_0_0_times.csv").read_text().splitlines()
         assert rows[0] == HEADER and len(rows) == 9, name
