@@ -25,6 +25,18 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(pytest.mark.skip(reason="needs >= 2 GPUs"))
 
 
+@pytest.fixture(scope="session", autouse=True)
+def _deterministic_cudnn():
+    """Several GPU tests train two copies of a model and compare them within a tolerance; cuDNN's
+    default backward kernels use atomics and are not run-to-run reproducible."""
+    import torch
+
+    if torch.cuda.is_available():
+        torch.backends.cudnn.deterministic = True
+        torch.backends.cudnn.benchmark = False
+    yield
+
+
 @pytest.fixture(scope="session")
 def free_port():
     import socket
