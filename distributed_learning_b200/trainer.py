@@ -226,6 +226,15 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
         save_checkpoint(ckpt, model, optimizer, batch_count, epoch, config)
 
     rows = timer.rows()
+    # one extra file next to the per-worker CSVs: every phase as the max over the ranks, which is
+    # how multi-GPU numbers of this project are quoted (the reference reports per-worker files only)
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1 and rows:
+        worst = timer.max_over_ranks()
+        if dist.get_rank() == 0:
+            with open(f"{config.folder}/{name}_max_over_ranks_times.csv", "w") as f:
+                f.write(PhaseTimer.format_csv(worst))
     model.cleanup()
     if reducer is not None and hasattr(reducer, "cleanup"):
         reducer.cleanup()

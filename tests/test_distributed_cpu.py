@@ -79,6 +79,10 @@ def test_experiment3_two_nodes_cpu_bit_identical_losses(free_port, tmp_path):
         assert head == ("experiment_name, get_data, data2dev, zero_grad, forward, backprop, sync, optimizer_step, "
                         "batch, batch_count, data_len")
         assert os.path.exists(os.path.join(folder, f"{n}_config.txt"))
+        worst = open(os.path.join(folder, f"{n}_max_over_ranks_times.csv")).read().splitlines()
+        assert worst[0] == head and len(worst) == 5
+        mine = [float(x) for x in open(os.path.join(folder, f"{n}_0_0_times.csv")).read().splitlines()[2].split(", ")[1:9]]
+        assert all(w >= m - 1e-9 for w, m in zip([float(x) for x in worst[2].split(", ")[1:9]], mine))
     assert os.path.exists(os.path.join(folder, "warmup_0_0_times.csv"))
 
 
