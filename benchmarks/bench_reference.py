@@ -12,7 +12,6 @@ string every step, which synchronises the device inside that span, so it is a tr
 from __future__ import annotations
 
 import csv
-import json
 import os
 import shutil
 import subprocess

@@ -27,7 +27,6 @@ import functools
 import os
 from typing import Callable, Dict
 
-import torch
 import torch.multiprocessing as mp
 
 from .parallel.allreduce import central_allreduce, ring_allreduce, ring_allreduce_gpu

@@ -22,7 +22,7 @@ All functions average ``send`` in place and accept an optional process ``group``
 """
 from __future__ import annotations
 
-from typing import List, Optional, Tuple
+from typing import List, Tuple
 
 import torch
 import torch.distributed as dist

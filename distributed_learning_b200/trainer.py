@@ -27,7 +27,6 @@ import os
 import sys
 import traceback
 from contextlib import nullcontext
-from typing import Optional
 
 import torch
 import torch.nn.functional as F

@@ -1,6 +1,5 @@
 """The command line on the native backend with one GPU, checkpoint/resume through FusedSGD, and the
 failure detection of the device-side barrier (needs a GPU)."""
-import ctypes
 import os
 import subprocess
 import sys
