@@ -2,7 +2,7 @@
 
 These are the *plumbing* and *baseline* algorithms (``--backend gloo`` and ``--backend nccl``);
 the product path is the in-kernel NVLink allreduce in ``csrc/allreduce.cu`` bound by
-``distributed_learning_b200.ops.allreduce``.
+``distributed_learning_b200.ops.comm.NativeComm``.
 
 Parity: reference ``src/allreduce.py``:
 
@@ -12,7 +12,8 @@ Parity: reference ``src/allreduce.py``:
   steps over ``torch.chunk`` pieces, sending to ``rank+1`` and receiving from ``rank-1``, then
   one division.  The chunk boundaries, ring direction and order of additions are the same, so
   on CPU the result is bit-identical to the reference's (checked against a plain restatement
-  of that arithmetic in ``tests/test_allreduce_cpu.py``).
+  of that arithmetic in ``tests/test_distributed_cpu.py``, and against the reference itself in
+  ``tests/test_reference_parity_cpu.py``).
 * ``ring_allreduce_gpu`` (``:100-170``): the reference emulates NCCL point-to-point with
   broadcasts in two-rank groups, and special-cases the last rank to avoid deadlock.  NCCL has
   had real send/recv for years, so here each ring step is one grouped

@@ -434,3 +434,75 @@ class FusedSGD:
                 if st is not None and st.get("momentum_buffer") is not None:
                     nb.momentum[off:off + t.numel()].copy_(st["momentum_buffer"].reshape(-1))
                     self.steps = max(self.steps, 1)
+
+
+class NativeReducer:
+    """The in-kernel NVLink allreduce behind the reference's reducer surface (``put`` / ``get`` /
+    ``cleanup``, ``src/reducers.py``), so that any host-driven wrapper (``OurDist``,
+    ``SeqMergeDist``, ``SeqDist``) can be combined with it -- the reference's "any wrapper with any
+    reducer and any allreduce".  ``put`` stages the buffer in the peer-mapped arena, averages it
+    across the ranks with one kernel and copies it back, all on the reducer's own stream; ``get``
+    makes the caller's stream wait for that.  ``B200Dist`` is the fast path (no staging copies, fused
+    update); this class exists for composability.
+
+    Buffers must be fp32 or bf16 CUDA tensors of at most ``capacity_bytes``.  Every rank must
+    ``put`` buffers of the same sizes in the same order."""
+
+    def __init__(self, comm: Optional[NativeComm] = None, capacity_bytes: int = 64 << 20, group=None, device=None):
+        import queue
+
+        self.owns_comm = comm is None
+        self.comm = comm if comm is not None else NativeComm(group, device)
+        self.capacity = _round_up(int(capacity_bytes), _REGION_ALIGN)
+        if self.comm.mode is None:
+            self.comm.allocate(self.capacity)
+        elif self.comm.nbytes - self.comm.data_offset < self.capacity:
+            raise RuntimeError("the communicator's arena is smaller than capacity_bytes")
+        self.device = self.comm.device
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.pending = queue.Queue()     # get() blocks until the matching put() has been issued (threaded wrappers)
+        self.launches = 0
+
+    def put(self, buff: torch.Tensor) -> None:
+        if not buff.is_cuda or buff.dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError("NativeReducer reduces fp32 or bf16 CUDA buffers")
+        if not buff.is_contiguous():
+            raise ValueError("NativeReducer needs a contiguous buffer (it is reduced in place)")
+        flat = buff.view(-1)
+        n, esize = flat.numel(), flat.element_size()
+        per_vec = 16 // esize
+        padded = _round_up(n, per_vec)
+        if padded * esize > self.capacity:
+            raise ValueError(f"buffer of {n * esize} bytes exceeds the reducer's capacity of {self.capacity}")
+        comm, world = self.comm, self.comm.world
+        with torch.cuda.device(self.device):
+            ready = torch.cuda.Event()
+            ready.record(torch.cuda.current_stream(self.device))
+            self.stream.wait_event(ready)
+            with torch.cuda.stream(self.stream):
+                if world > 1:
+                    view = comm.view(0, padded, buff.dtype)
+                    view[:n].copy_(flat)
+                    if padded > n:
+                        view[n:].zero_()
+                    algo, nblocks = comm.choose(padded * esize, buff.dtype, "auto")
+                    if algo == "oneshot":        # in place, and safe to refill right away
+                        algo = "twoshot"
+                    comm.allreduce(0, padded, buff.dtype, algo, 1.0 / world, nblocks=nblocks, stream=self.stream)
+                    flat.copy_(view[:n])
+                    self.launches += 1
+                done = torch.cuda.Event()
+                done.record(self.stream)
+        self.pending.put((buff, done))
+
+    def get(self) -> torch.Tensor:
+        buff, done = self.pending.get()
+        torch.cuda.current_stream(self.device).wait_event(done)
+        return buff
+
+    def cleanup(self) -> None:
+        torch.cuda.synchronize(self.device)
+        if self.comm.mode is not None:
+            self.comm.check()
+            if self.owns_comm:
+                self.comm.close()

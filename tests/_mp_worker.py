@@ -121,6 +121,44 @@ def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overl
     w.cleanup()
 
 
+def check_native_reducer(rank, world, dev):
+    """OurDist (threads, host-driven) over NativeReducer equals manual allreduce + SGD."""
+    from distributed_learning_b200.models import CifarNet
+    from distributed_learning_b200.parallel.native import NativeReducer
+    from distributed_learning_b200.parallel.wrappers import OurDist
+
+    torch.manual_seed(13)
+    ref = CifarNet().to(dev).train()
+    mine = CifarNet().to(dev).train()
+    mine.load_state_dict(ref.state_dict())
+    for mdl in (ref, mine):
+        mdl.dropout1.p = mdl.dropout2.p = 0.0
+    reducer = NativeReducer(capacity_bytes=8 << 20, device=dev)
+    w = OurDist(mine, reducer, 256 * 1024, dev)
+    opt = torch.optim.SGD(mine.parameters(), lr=0.01, momentum=0.5)
+    ref_opt = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.5)
+    g = torch.Generator(device=dev).manual_seed(900 + rank)
+    for _ in range(3):
+        x = torch.rand(8, 3, 32, 32, device=dev, generator=g)
+        y = torch.randint(10, (8,), device=dev, generator=g)
+        opt.zero_grad()
+        F.nll_loss(w(x), y).backward()
+        w.sync_gradients()
+        opt.step()
+        ref_opt.zero_grad()
+        F.nll_loss(ref(x), y).backward()
+        for p in ref.parameters():
+            dist.all_reduce(p.grad)
+            p.grad /= world
+        ref_opt.step()
+    torch.cuda.synchronize()
+    for (n, p), q in zip(mine.named_parameters(), ref.parameters()):
+        if not torch.allclose(p, q, rtol=1e-4, atol=1e-5):
+            raise AssertionError(f"rank {rank}: OurDist+NativeReducer: parameter {n} diverged")
+    w.cleanup()
+    reducer.cleanup()
+
+
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -150,6 +188,8 @@ def main():
                    dict(model_dtype="bf16"), dict(graph=True), dict(graph=True, algo="oneshot"),
                    dict(graph=True, algo="twoshot", fused=False)):
             check_training(rank, world, dev, None, **kw)
+    if what in ("all", "train"):
+        check_native_reducer(rank, world, dev)
     dist.barrier()
     if rank == 0:
         print("MP_WORKER_OK")
