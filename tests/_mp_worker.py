@@ -188,7 +188,7 @@ def main():
                    dict(model_dtype="bf16"), dict(graph=True), dict(graph=True, algo="oneshot"),
                    dict(graph=True, algo="twoshot", fused=False)):
             check_training(rank, world, dev, None, **kw)
-    if what in ("all", "train"):
+    if what in ("all", "train", "reducer"):
         check_native_reducer(rank, world, dev)
     dist.barrier()
     if rank == 0:
