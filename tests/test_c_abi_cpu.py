@@ -1,0 +1,50 @@
+"""The header is plain C and the library is usable from a C program (no Python, no torch)."""
+import os
+import shutil
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+C_PROGRAM = r"""
+#include <stdio.h>
+#include <string.h>
+#include "dlb200.h"
+
+int main(void) {
+    char topo[4096];
+    int count = -1;
+    dlb_sgd_hyper_t h = {0.01f, 0.5f, 0.0f, 0.0f, 1.0f, 0};
+    dlb_fused_sgd_t f;
+    memset(&f, 0, sizeof f);
+    f.hyper = h;
+    if (dlb_version() < 100) return 1;
+    if (dlb_emulated_flags_bytes(8) != 8u * (DLB_SIGNAL_BYTES + 4 * DLB_STATE_WORDS)) return 2;
+    if (dlb_emulated_static_scratch_bytes() != dlb_emulated_flags_bytes(DLB_MAX_RANKS)) return 3;
+    if (dlb_topology_json(topo, sizeof topo) != 0 || strstr(topo, "\"devices\"") == NULL) return 4;
+    /* argument checking happens before any CUDA call, so it works without a GPU */
+    if (dlb_pack(NULL, 99, NULL, NULL, NULL, NULL, 0, 1.0f, NULL) != DLB_E_ARG) return 5;
+    if (strstr(dlb_last_error(), "dtype") == NULL) return 6;
+    (void)dlb_device_count(&count);
+    printf("ok version=%d devices=%d sgd_args=%zu bytes\n", dlb_version(), count, sizeof f);
+    return 0;
+}
+"""
+
+
+@pytest.mark.skipif(shutil.which("gcc") is None, reason="no C compiler")
+def test_header_is_c_and_library_links_from_c(tmp_path):
+    from distributed_learning_b200.ops import _lib
+
+    _lib.lib()                                   # builds the library if it is missing
+    libdir = os.path.dirname(_lib.library_path())
+    src = tmp_path / "abi.c"
+    src.write_text(C_PROGRAM)
+    exe = tmp_path / "abi"
+    cc = subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                         "-L", libdir, "-ldlb200", f"-Wl,-rpath,{libdir}"], capture_output=True, text=True)
+    assert cc.returncode == 0, cc.stderr
+    run = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert run.returncode == 0, (run.returncode, run.stdout, run.stderr)
+    assert run.stdout.startswith("ok version=")
