@@ -33,7 +33,9 @@ def _losses(path):
     return vals
 
 
-@pytest.mark.parametrize("experiment,name", [("main_onestep_reduce", "onestep_reduce"), ("main_onestep_seq_merge", "onestep_seq_merge")])
+# one experiment is enough here: test_distributed_cpu.py shows that all of this framework's algorithms
+# give bit-identical trajectories among themselves
+@pytest.mark.parametrize("experiment,name", [("main_onestep_reduce", "onestep_reduce")])
 def test_same_loss_trajectory_as_the_reference(tmp_path, free_port, experiment, name):
     from distributed_learning_b200.utils.data import write_fake_mnist
 
