@@ -57,7 +57,7 @@ def save_checkpoint(path: str, model, optimizer, batch_count: int, epoch: int = 
 
 def load_checkpoint(path: str, model=None, optimizer=None, map_location="cpu", restore_rng: bool = False) -> Dict[str, Any]:
     """Load ``path``; restore ``model`` / ``optimizer`` in place when given.  Returns the payload."""
-    payload = torch.load(path, map_location=map_location, weights_only=False)
+    payload = torch.load(path, map_location=map_location, weights_only=True)   # tensors and plain containers only
     if payload.get("format") != FORMAT:
         raise ValueError(f"{path}: unknown checkpoint format {payload.get('format')!r}")
     if model is not None:
