@@ -98,6 +98,10 @@ def finalize_config(config: argparse.Namespace) -> argparse.Namespace:
         config.sync_loss = 0 if config.use_gpu == 1 else 1
     if config.backend == "b200" and config.use_gpu != 1:
         raise SystemExit("--backend b200 is the NVLink path: it needs g=1 (use --backend gloo on the CPU)")
+    if getattr(config, "cuda_graph", 0) and int(config.random_input) == 3:
+        # the prefetcher's staging thread pins host memory while the step is being captured, which
+        # a global-mode capture does not allow; bench.py shows the supported order (capture first)
+        raise SystemExit("--cuda_graph 1 cannot be combined with --random_input 3 in main.py; use --random_input 1 or 2")
     if config.backend == "b200" and config.total_dev > 8:
         raise SystemExit("--backend b200 spans one NVSwitch domain (at most 8 GPUs); use --backend nccl beyond that")
     if config.size * config.node_dev != config.total_dev:
