@@ -88,6 +88,8 @@ def main():
         print(f"arena {comm.mode}, multicast {comm.has_multicast} {comm.mc_note}", flush=True)
     blocks = [int(b) for b in args.blocks.split(",")]
     algos = ["oneshot", "twoshot"] + (["nvls"] if comm.has_multicast else [])
+    if comm.has_multicast and os.environ.get("DLB200_EXPERIMENTAL"):
+        algos.append("nvls_deep")
     rows = []
     size = args.min_bytes
     while size <= args.max_bytes:

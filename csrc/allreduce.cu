@@ -565,3 +565,96 @@ extern "C" int dlb_allreduce_emulated_static(int algo, void* const* bufs, void* 
     DLB_CUDA(cudaMemsetAsync(flags, 0, used, (cudaStream_t)stream));
     return dlb_allreduce_emulated(algo, bufs, outs, nullptr, flags, nranks, numel, dtype, scale, nblocks, nthreads, stream);
 }
+
+// ---- EXPERIMENTAL: nvls with a deeper load pipeline ---------------------------------------------------
+//
+// Not selected by default and not yet measured on hardware (written after this round's GPU budget
+// was spent; `--algo nvls_deep` or DLB200_EXPERIMENTAL=1 opts in).  Motivation, from the 8-GPU sweep:
+// nvls_kernel shares its tile (blockDim x 2 vectors for 8 ranks) with the two-shot kernel so both can
+// use one epilogue partition, which leaves two multimem.ld_reduce in flight per thread, and the
+// tuner prefers 8-16 CTAs at 4-16 MiB: the variant is latency-bound there (29 % / 59 % of the NVLink
+// roofline).  Here the tile is blockDim x 8 vectors with all eight switch reductions issued before
+// the first multimem.st, and the epilogue walks the same larger tiles, so the same-numbered-CTA
+// argument for the barrier still holds.
+namespace {
+
+template <typename T, int NR>
+__global__ void __launch_bounds__(512, 1) nvls_deep_kernel(const __grid_constant__ CommArgs a) {
+    constexpr int N = VecOf<T>::N;
+    constexpr int U = 8;
+    const int nr = ranks_of<NR>(a);
+    const int rank = a.rank;
+    uint32_t* state = a.state;
+    uint32_t* err = state + DLB_MAX_BLOCKS;
+    uint32_t epoch = state[blockIdx.x];
+
+    block_barrier<NR>(a, rank, ++epoch, err);
+
+    const int64_t slice = (a.nvec + nr - 1) / nr;
+    const int64_t begin = rank * slice, end = min(begin + slice, a.nvec);
+    const int64_t tile = (int64_t)blockDim.x * U;
+    char* mc = reinterpret_cast<char*>(a.mc);
+    for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < slice; t0 += (int64_t)gridDim.x * tile) {
+        float acc[U][N];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t j = begin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
+            if (j < end) multimem_ld_reduce<T>(mc + j * 16, acc[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t j = begin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
+            if (j < end) {
+#pragma unroll
+                for (int i = 0; i < N; ++i) acc[u][i] *= a.scale;
+                multimem_st<T>(mc + j * 16, acc[u]);
+            }
+        }
+    }
+
+    block_barrier<NR>(a, rank, ++epoch, err);
+
+    if (a.has_sgd) {
+        const char* local = reinterpret_cast<const char*>(a.buf[rank]);
+        for (int sl = 0; sl < nr; ++sl) {
+            const int64_t sbegin = sl * slice, send = min(sbegin + slice, a.nvec);
+            for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < slice; t0 += (int64_t)gridDim.x * tile) {
+#pragma unroll 2
+                for (int u = 0; u < U; ++u) {
+                    const int64_t j = sbegin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
+                    if (j < send) {
+                        float g[N];
+                        VecOf<T>::to_float(ld_vec(local + j * 16), g);
+                        sgd_apply_vec<N>(a.sgd[0], (size_t)j * N, g);
+                    }
+                }
+            }
+        }
+    }
+    if (threadIdx.x == 0) state[blockIdx.x] = epoch;
+}
+
+template <typename T>
+KernelFn pick_nvls_deep(int nranks) {
+    switch (nranks) {
+        case 2: return nvls_deep_kernel<T, 2>;
+        case 4: return nvls_deep_kernel<T, 4>;
+        case 8: return nvls_deep_kernel<T, 8>;
+        default: return nvls_deep_kernel<T, 0>;
+    }
+}
+
+}  // namespace
+
+extern "C" int dlb_allreduce_nvls_deep(void* mc_buf, void* const* bufs, void* const* sigs, uint32_t* state, int rank,
+                                       int nranks, int64_t numel, int dtype, float scale, int nblocks, int nthreads,
+                                       const dlb_fused_sgd_t* sgd, void* stream) {
+    CommArgs a;
+    DLB_REQUIRE(bufs != nullptr && mc_buf != nullptr, DLB_E_ARG, "dlb_allreduce_nvls_deep: null buffer");
+    DLB_REQUIRE((reinterpret_cast<uintptr_t>(mc_buf) & 15) == 0, DLB_E_ARG, "dlb_allreduce_nvls_deep: multicast pointer not 16-byte aligned");
+    int rc = fill_args(a, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd, "dlb_allreduce_nvls_deep");
+    if (rc || a.nvec == 0) return rc;
+    a.mc = mc_buf;
+    KernelFn k = dtype == DLB_F32 ? pick_nvls_deep<float>(nranks) : pick_nvls_deep<__nv_bfloat16>(nranks);
+    return launch(k, dim3(nblocks), nthreads, (cudaStream_t)stream, a, false);
+}

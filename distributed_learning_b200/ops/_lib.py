@@ -86,6 +86,8 @@ _PROTOS = {
                                       c_int, c_float, c_int, c_int, c_int, POINTER(FusedSgd), c_void_p]),
     "dlb_allreduce_nvls": (c_int, [c_void_p, POINTER(c_void_p), POINTER(c_void_p), c_void_p, c_int, c_int, c_int64,
                                    c_int, c_float, c_int, c_int, POINTER(FusedSgd), c_void_p]),
+    "dlb_allreduce_nvls_deep": (c_int, [c_void_p, POINTER(c_void_p), POINTER(c_void_p), c_void_p, c_int, c_int, c_int64,
+                                        c_int, c_float, c_int, c_int, POINTER(FusedSgd), c_void_p]),
     "dlb_barrier": (c_int, [POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_void_p]),
     "dlb_set_wait_timeout_ms": (c_int, [c_int]),
     "dlb_comm_check": (c_int, [c_void_p, c_void_p]),

@@ -271,7 +271,7 @@ class NativeComm:
         """Variant and grid for a message: the measured table if ``tune`` filled it, else a
         size heuristic (one-shot while latency dominates, NVLS when the switch can reduce)."""
         if algo != "auto":
-            if algo == "nvls" and not self.has_multicast:
+            if algo in ("nvls", "nvls_deep") and not self.has_multicast:
                 algo = "twoshot"
             return algo, default_nblocks(nbytes, algo)
         key = (dtype_code(dtype), max(nbytes, 1).bit_length())
@@ -308,10 +308,11 @@ class NativeComm:
             out = self.peer_ptrs[self.rank] + self.data_offset + out_offset if out_offset is not None else None
             check(L.dlb_allreduce_oneshot(self._bufs(offset), out, self._sig_array, self.state.data_ptr(), self.rank,
                                           self.world, numel, code, scale, nblocks, self.nthreads, int(end_barrier), sgd_p, st))
-        elif algo == "nvls":
+        elif algo in ("nvls", "nvls_deep"):
             if not self.has_multicast:
                 raise RuntimeError("nvls requested but no multicast mapping exists")
-            check(L.dlb_allreduce_nvls(self.mc_ptr + self.data_offset + offset, self._bufs(offset), self._sig_array,
+            fn = L.dlb_allreduce_nvls if algo == "nvls" else L.dlb_allreduce_nvls_deep     # the latter is experimental
+            check(fn(self.mc_ptr + self.data_offset + offset, self._bufs(offset), self._sig_array,
                                        self.state.data_ptr(), self.rank, self.world, numel, code, scale, nblocks,
                                        self.nthreads, sgd_p, st))
         else:
@@ -338,6 +339,8 @@ class NativeComm:
         stream = torch.cuda.current_stream(self.device)
         report: Dict[int, dict] = {}
         algos = [a for a in ALGOS if a != "nvls" or self.has_multicast]
+        if self.has_multicast and os.environ.get("DLB200_EXPERIMENTAL"):
+            algos.append("nvls_deep")            # opt-in: not yet measured on hardware
         for nbytes in sizes_bytes:
             nbytes = _round_up(nbytes, 16)
             numel = nbytes // esize

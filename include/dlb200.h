@@ -154,6 +154,11 @@ int dlb_allreduce_oneshot(void* const* bufs, void* out, void* const* sigs, uint3
 int dlb_allreduce_nvls(void* mc_buf, void* const* bufs, void* const* sigs, uint32_t* state, int rank, int nranks,
                        int64_t numel, int dtype, float scale, int nblocks, int nthreads,
                        const dlb_fused_sgd_t* sgd, void* stream);
+/* EXPERIMENTAL, not selected by default and not yet measured on hardware: dlb_allreduce_nvls with
+ * eight multimem.ld_reduce in flight per thread instead of two (same arguments, same result). */
+int dlb_allreduce_nvls_deep(void* mc_buf, void* const* bufs, void* const* sigs, uint32_t* state, int rank, int nranks,
+                            int64_t numel, int dtype, float scale, int nblocks, int nthreads,
+                            const dlb_fused_sgd_t* sgd, void* stream);
 /* device-side barrier on its own (used at bring-up and by tests) */
 int dlb_barrier(void* const* sigs, uint32_t* state, int rank, int nranks, int nblocks, void* stream);
 /* spin budget of the device-side waits in milliseconds (default 20000; 0 = wait forever) */

@@ -23,6 +23,8 @@ def check_allreduce(comm, rank, world, dev):
     from distributed_learning_b200.ops import fused as K
 
     algos = ["twoshot", "oneshot"] + (["nvls"] if comm.has_multicast else [])
+    if comm.has_multicast and os.environ.get("DLB200_EXPERIMENTAL"):
+        algos.append("nvls_deep")
     for dtype in (torch.float32, torch.bfloat16):
         esize = 4 if dtype == torch.float32 else 2
         for numel in (16, 4096, 100000 // 8 * 8, 1 << 22):
@@ -37,7 +39,7 @@ def check_allreduce(comm, rank, world, dev):
                     comm.allreduce(0, numel, dtype, algo, scale=1.0 / world, out_offset=out_off)
                     res = comm.view(out_off, numel, dtype) if algo == "oneshot" else buf
                     torch.cuda.synchronize()
-                    if algo == "nvls":
+                    if algo.startswith("nvls"):
                         ok = torch.allclose(res.float(), want.float(), rtol=2e-2 if esize == 2 else 1e-5, atol=1e-2 if esize == 2 else 1e-5)
                     else:
                         ok = torch.equal(res, want)
@@ -63,7 +65,7 @@ def check_allreduce(comm, rank, world, dev):
                            sgd=K.fused_sgd_args(p, m, h))
             torch.cuda.synchronize()
             dist.barrier()
-        tol = 1e-5 if algo == "nvls" else 1e-6
+        tol = 1e-5 if algo.startswith("nvls") else 1e-6
         if not torch.allclose(p, ref_p.detach(), rtol=tol, atol=tol):
             raise AssertionError(f"rank {rank}: fused sgd via {algo} diverged: {(p - ref_p).abs().max().item()}")
 
