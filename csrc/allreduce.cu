@@ -18,7 +18,7 @@
 //             broadcasts the result through the switch: about S/N + S per direction.
 //
 // Device-side barrier: rank r's CTA b writes an epoch number into slot [b][r] of every peer's
-// signal pad (st.release.sys after a system fence) and spins (ld.acquire.sys) on its own pad's
+// signal pad (st.release.sys after a CTA barrier) and spins (ld.acquire.sys) on its own pad's
 // slots [b][*].  Epochs only grow, the comparison is wrap-safe, a rank can be at most one
 // barrier ahead of a peer, so one slot per (CTA, peer) is enough and nothing is ever reset.
 // The epoch counter lives in device memory, so launches can be captured in a CUDA graph.
