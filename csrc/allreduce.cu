@@ -33,6 +33,8 @@
 //
 // Fused epilogue: with `sgd` set, the reduced gradient is consumed by the SGD-momentum update
 // in the same kernel -- straight from registers in the one-shot variant.
+#include <stdlib.h>
+
 #include "sgd_math.cuh"
 
 namespace {
@@ -50,7 +52,21 @@ struct CommArgs {
     int rank, nranks, end_barrier, has_sgd;
 };
 
-uint64_t g_timeout_ns = 20000ull * 1000000ull;
+// 10 minutes, the order of NCCL's watchdog: long enough for a rank that is still loading data or
+// timing cuDNN algorithms, short enough that a dead peer ends the job.  $DLB200_WAIT_TIMEOUT_MS overrides.
+uint64_t g_timeout_ns = 600000ull * 1000000ull;
+bool g_timeout_env_read = false;
+
+uint64_t wait_timeout_ns() {
+    if (!g_timeout_env_read) {
+        g_timeout_env_read = true;
+        if (const char* e = getenv("DLB200_WAIT_TIMEOUT_MS")) {
+            const long long ms = atoll(e);
+            g_timeout_ns = ms <= 0 ? 0ull : (uint64_t)ms * 1000000ull;
+        }
+    }
+    return g_timeout_ns;
+}
 
 template <int NR>
 __device__ __forceinline__ int ranks_of(const CommArgs& a) {
@@ -341,7 +357,7 @@ int fill_args(CommArgs& a, void* const* bufs, void* const* sigs, uint32_t* state
     a.state = state;
     a.mc = nullptr;
     a.nvec = numel / per_vec;
-    a.timeout_ns = g_timeout_ns;
+    a.timeout_ns = wait_timeout_ns();
     a.scale = scale;
     a.rank = rank;
     a.nranks = nranks;
@@ -396,6 +412,7 @@ KernelFn pick_nvls(int nranks) {
 }  // namespace
 
 extern "C" int dlb_set_wait_timeout_ms(int ms) {
+    g_timeout_env_read = true;      // an explicit call wins over the environment
     g_timeout_ns = ms <= 0 ? 0ull : (uint64_t)ms * 1000000ull;
     return 0;
 }

@@ -29,7 +29,7 @@ DEFAULT_EPOCH_COUNT = 100
 DEFAULT_MASTER_PORT = 29501
 
 MODEL_TYPES = ("mnist", "cifar", "imagenet", "googlenet", "resnet50")
-BACKENDS = ("gloo", "nccl", "b200", "mpi")
+BACKENDS = ("gloo", "nccl", "b200")
 
 
 def build_parser() -> argparse.ArgumentParser:

@@ -161,7 +161,7 @@ int dlb_allreduce_nvls_deep(void* mc_buf, void* const* bufs, void* const* sigs, 
                             const dlb_fused_sgd_t* sgd, void* stream);
 /* device-side barrier on its own (used at bring-up and by tests) */
 int dlb_barrier(void* const* sigs, uint32_t* state, int rank, int nranks, int nblocks, void* stream);
-/* spin budget of the device-side waits in milliseconds (default 20000; 0 = wait forever) */
+/* spin budget of the device-side waits in milliseconds (default 600000, or $DLB200_WAIT_TIMEOUT_MS; 0 = wait forever) */
 int dlb_set_wait_timeout_ms(int ms);
 /* reads the error word of `state` (synchronises `stream`); 0 or DLB_E_TIMEOUT */
 int dlb_comm_check(uint32_t* state, void* stream);
