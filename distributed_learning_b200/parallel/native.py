@@ -143,6 +143,44 @@ class B200Dist(_Wrapper):
                 if t.dtype == torch.bfloat16:
                     nb.master[off:off + t.numel()].copy_(t.detach().reshape(-1))
 
+    def master_state_dict(self) -> Dict[str, torch.Tensor]:
+        """fp32 master copies of the bf16 parameters, keyed like ``model.state_dict()`` (empty for an
+        fp32 model, whose parameters are their own masters).  Stored in checkpoints so a bf16 run
+        resumes without losing the low bits of its master weights."""
+        names = {id(p): n for n, p in self.model.named_parameters()}
+        out: Dict[str, torch.Tensor] = {}
+        if self.buckets is None:
+            for p, master in (self._fp32_stash or {}).items():
+                out[names[id(p)]] = master.detach().clone()
+            return out
+        for nb in self.buckets:
+            if nb.shadow is None:
+                continue
+            for t, off in zip(nb.tensors, nb.b.offsets):
+                if t.dtype == torch.bfloat16:
+                    out[names[id(t)]] = nb.master[off:off + t.numel()].view(t.shape).clone()
+        return out
+
+    def load_master_state_dict(self, sd: Optional[Dict[str, torch.Tensor]]) -> None:
+        """Inverse of ``master_state_dict``; call after the (bf16) parameters were restored."""
+        if not sd:
+            return
+        by_name = dict(self.model.named_parameters())
+        if self.buckets is None:
+            if self._fp32_stash is not None:
+                for n, v in sd.items():
+                    p = by_name.get(n)
+                    if p is not None and p in self._fp32_stash:
+                        self._fp32_stash[p] = v.detach().to(p.device, torch.float32)
+            return
+        names = {id(p): n for n, p in by_name.items()}
+        with torch.no_grad():
+            for nb in self.buckets:
+                for t, off in zip(nb.tensors, nb.b.offsets):
+                    v = sd.get(names[id(t)])
+                    if v is not None and t.dtype == torch.bfloat16:
+                        nb.master[off:off + t.numel()].copy_(v.reshape(-1))
+
     def _probe_unused(self, data) -> List[torch.Tensor]:
         """One throw-away forward to find parameters the loss does not reach; RNG state and
         module buffers (BatchNorm statistics) are restored so the real step is unaffected."""

@@ -5,7 +5,9 @@ The reference has no checkpointing at all (no ``state_dict``, ``t
 by worker 0 of node 0 (all replicas hold identical state after every step):
 
 ``{"format": 1, "model": model.state_dict(), "optimizer": optimizer.state_dict(),
-   "batch_count": int, "epoch": int, "config": {...plain values...}, "rng": {...}}``
+   "batch_count": int, "epoch": int, "config": {...plain values...}, "rng": {...},
+   "master_fp32": {...}}``  (the last entry only carries data for bf16 models on the native path:
+   their fp32 master weights)
 
 The optimizer entry has ``torch.optim.SGD``'s layout (``param_groups`` +
 ``state[i]["momentum_buffer"]``) whichever optimizer wrote it, so a run can be resumed under a
@@ -46,6 +48,10 @@ def save_checkpoint(path: str, model, optimizer, batch_count: int, epoch: int = 
         "config": cfg,
         "rng": {"torch": torch.get_rng_state()},
     }
+    masters = getattr(model, "master_state_dict", None)
+    if callable(masters):
+        # bf16 models on the native path: the fp32 master weights, so a resume loses no precision
+        payload["master_fp32"] = _to_cpu(masters())
     if extra:
         payload["extra"] = extra
     os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
@@ -73,6 +79,9 @@ def load_checkpoint(path: str, model=None, optimizer=None, map_location="cpu", r
         refresh = getattr(model, "parameters_were_reloaded", None)
         if callable(refresh):
             refresh()
+        restore = getattr(model, "load_master_state_dict", None)
+        if callable(restore) and payload.get("master_fp32"):
+            restore(payload["master_fp32"])
     if optimizer is not None and payload.get("optimizer") is not None:
         optimizer.load_state_dict(payload["optimizer"])
     if restore_rng and "rng" in payload:
