@@ -32,6 +32,9 @@ sys.path.insert(0, ROOT)
 
 # DDP images/sec of the reference on P100s (gloo), GoogLeNet batch 128/GPU
 PUBLISHED_DDP = {1: 299.0, 2: 575.2, 4: 1106.5, 8: 2198.2, 16: 4362.5}
+# One metric string for BOTH arms (the driver compares them field by field); how each arm times its
+# steps is in config.timing.
+METRIC = "images/sec (training throughput, data parallel, max over ranks)"
 MODEL_ALIASES = {"googlenet": "imagenet", "imagenet": "imagenet", "resnet50": "resnet50", "mnist": "mnist",
                  "basicnet": "mnist", "cifar": "cifar"}
 
@@ -115,6 +118,33 @@ class ClockSampler:
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def baseline_fields(value, e2e_value, model_type, per_gpu_batch, world, dtype) -> dict:
+    """`vs_baseline` is value / the number BASELINE.md publishes for this config: the reference's DDP
+    run on P100s over gloo (section 2) -- mostly a statement about hardware generations.  The
+    same-hardware context sits next to it: the unmodified reference and torch DDP-NCCL as measured
+    on this pool's B200 box (benchmarks/same_hw_reference.json)."""
+    out = {"vs_baseline": None, "vs_baseline_is": "value / BASELINE.md section 2 (reference DDP on P100 + gloo, published CSVs)"}
+    if not (model_type == "imagenet" and per_gpu_batch == 128 and dtype == "fp32"):
+        return out
+    if world in PUBLISHED_DDP:
+        out["vs_baseline"] = value / PUBLISHED_DDP[world]
+    try:
+        with open(os.path.join(ROOT, "benchmarks", "same_hw_reference.json")) as f:
+            same = json.load(f)["googlenet_fp32_b128"]
+    except (OSError, KeyError, ValueError):
+        return out
+    ref = same["reference_main_ddp_nccl_images_per_s"].get(str(world))
+    ddp = same["torch_ddp_nccl_same_layout_images_per_s"].get(str(world))
+    if ref:
+        out["vs_reference_same_hw"] = value / ref
+        if e2e_value:
+            out["e2e_vs_reference_same_hw"] = e2e_value / ref
+    if ddp:
+        out["vs_ddp_nccl_same_hw"] = value / ddp
+    out["same_hw_source"] = "benchmarks/same_hw_reference.json (round-1 driver run on this pool)"
+    return out
 
 
 def dist_env():

@@ -20,12 +20,21 @@ def _make_step(wrapper, opt):
     return step
 
 
-def _timed(batches, k, device, clocks=None):
-    """Exactly k steps between two events, barrier + synchronize on both sides; returns ms."""
-    torch.cuda.synchronize(device)
-    if dist.is_initialized():
-        dist.barrier()
-    torch.cuda.synchronize(device)
+def _timed(batches, k, device, clocks=None, comm=None):
+    """Exactly k steps between two events, barrier + synchronize on both sides; returns ms.
+
+    The host barrier goes over gloo (no NCCL communicator exists in this arm); the device-side
+    barrier kernel of the native communicator then lines the GPUs up, so the first event of every
+    rank is recorded within a few microseconds of its peers'."""
+    def barrier():
+        torch.cuda.synchronize(device)
+        if dist.is_initialized():
+            dist.barrier()
+            if comm is not None and comm.mode is not None and comm.world > 1:
+                comm.barrier()
+        torch.cuda.synchronize(device)
+
+    barrier()
     if clocks is not None:
         clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -33,9 +42,7 @@ def _timed(batches, k, device, clocks=None):
     for i in range(k):
         batches(i)
     e1.record()
-    torch.cuda.synchronize(device)
-    if dist.is_initialized():
-        dist.barrier()
+    barrier()
     stats = clocks.stop() if clocks is not None else None
     return e0.elapsed_time(e1), stats
 
@@ -44,7 +51,7 @@ def run(args, helpers) -> dict:
     from distributed_learning_b200.models import create_network
     from distributed_learning_b200.parallel.native import B200Dist
     from distributed_learning_b200.trainer import broadcast_initial_state
-    from distributed_learning_b200.utils.data import INPUT_SPECS, PinnedPrefetcher
+    from distributed_learning_b200.utils.data import INPUT_SPECS, NativeHostRandom, PinnedPrefetcher
 
     rank, local_rank, world = helpers.dist_env()
     if world != args.gpus:
@@ -53,7 +60,9 @@ def run(args, helpers) -> dict:
     torch.cuda.set_device(device)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world)
+        # gloo only: it carries the bootstrap (handle exchange, host barriers, the max over ranks);
+        # everything on the GPUs goes through this framework's own kernels, NCCL is never initialised
+        dist.init_process_group("gloo", rank=rank, world_size=world)
 
     model_type = helpers.MODEL_ALIASES[args.model]
     dtype = args.dtype or ("bf16" if model_type == "resnet50" else "fp32")
@@ -89,7 +98,8 @@ def run(args, helpers) -> dict:
     for i in range(args.warmup):
         step(*pool[i % pool_n])
     launches0 = wrapper.kernel_launches
-    ms, clocks = _timed(lambda i: step(*pool[i % pool_n]), args.steps, device, helpers.ClockSampler(local_rank))
+    ms, clocks = _timed(lambda i: step(*pool[i % pool_n]), args.steps, device, helpers.ClockSampler(local_rank),
+                        comm=wrapper.comm)
     launches = wrapper.kernel_launches - launches0
     ms = helpers.max_over_ranks(ms)
     images = bs * world * args.steps
@@ -97,43 +107,55 @@ def run(args, helpers) -> dict:
 
     e2e = None
     if not args.no_e2e:
-        # end to end through the public API: pinned host batches -> PinnedPrefetcher (H2D every
-        # step) -> wrapper/optimizer -> loss read back to the host every step
-        host_pool = [(torch.rand((bs,) + shape).contiguous(memory_format=fmt).pin_memory(),
-                      torch.randint(classes, (bs,)).pin_memory()) for _ in range(min(pool_n, 4))]
-
-        def host_batches():
-            i = 0
-            while True:
-                yield host_pool[i % len(host_pool)]
-                i += 1
-
-        pref = PinnedPrefetcher(host_batches(), device, depth=2, data_dtype=in_dtype,
-                                channels_last=bool(args.channels_last))
+        # End to end through the public API, doing the job the reference's step does: every step a
+        # FRESH random batch is produced on the host (native multi-threaded generator writing the
+        # pinned slot, csrc/hostgen.cpp), copied host->device by PinnedPrefetcher, trained on, and
+        # the loss is read back to the host.
+        src = NativeHostRandom((bs,) + shape, classes, seed=4321 + rank, dtype=torch.float32)
+        pref = PinnedPrefetcher(src, device, depth=3, data_dtype=in_dtype, channels_last=bool(args.channels_last))
         losses = []
 
         def e2e_step(_i):
             data, target = next(pref)
             losses.append(step(data, target).item())
 
-        for i in range(2):
+        for i in range(3):
             e2e_step(i)
-        ms2, _ = _timed(e2e_step, args.steps, device)
+        ms2, clocks2 = _timed(e2e_step, args.steps, device, helpers.ClockSampler(local_rank), comm=wrapper.comm)
         ms2 = helpers.max_over_ranks(ms2)
+        pref.close()
         e2e = {"value": images / (ms2 / 1000.0), "unit": "images/s", "ms_per_step": ms2 / args.steps,
                "h2d_bytes_per_step": pref.h2d_bytes_per_step, "d2h_bytes_per_step": 4,
-               "last_loss": losses[-1] if losses else None}
+               "input": f"fresh batch every step: native host generator ({src.nthreads} threads) -> pinned slot -> H2D",
+               "last_loss": losses[-1] if losses else None, "clocks": clocks2}
+
+        # second, labelled number: the same loop with the batch generated on the device
+        # (--random_input 1 of this framework); no H2D copy, so it is NOT the end-to-end figure
+        gd = torch.Generator(device=device).manual_seed(99 + rank)
+
+        def dev_step(_i):
+            data = torch.rand((bs,) + shape, device=device, generator=gd).to(in_dtype).contiguous(memory_format=fmt)
+            target = torch.randint(classes, (bs,), device=device, generator=gd)
+            losses.append(step(data, target).item())
+
+        for i in range(2):
+            dev_step(i)
+        ms3, _ = _timed(dev_step, args.steps, device, comm=wrapper.comm)
+        ms3 = helpers.max_over_ranks(ms3)
+        e2e["device_rng_variant"] = {"value": images / (ms3 / 1000.0), "unit": "images/s",
+                                     "ms_per_step": ms3 / args.steps, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4,
+                                     "input": "fresh batch every step generated on the device (torch.rand), loss read back"}
 
     wrapper.comm.check()
     buckets = [{"mib": round(nb.numel * nb.regions[0].element_size() / 2**20, 2), "algo": nb.algo, "nblocks": nb.nblocks}
                for nb in wrapper.buckets]
     result = {
-        "metric": "training images/sec (GoogLeNet-class CNN, data parallel, device-timed, max over ranks)",
+        "metric": helpers.METRIC,
         "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": (value / helpers.PUBLISHED_DDP[world]) if (model_type == "imagenet" and bs == 128 and world in helpers.PUBLISHED_DDP) else None,
         "dtype": dtype, "data": "synthetic (random images of the named shape, random-init weights)",
         "impl": "b200",
+        **helpers.baseline_fields(value, e2e["value"] if e2e else None, model_type, bs, world, dtype),
         "config": {"model": {"imagenet": "googlenet(aux heads)", "resnet50": "resnet50", "mnist": "basicnet-mnist",
                              "cifar": "basicnet-cifar"}[model_type],
                    "global_batch": bs * world, "per_gpu_batch": bs, "seq_len": None,
@@ -143,6 +165,9 @@ def run(args, helpers) -> dict:
                    "multicast_note": wrapper.comm.mc_note,
                    "channels_last": bool(args.channels_last), "cudnn_benchmark": bool(args.cudnn_benchmark),
                    "cuda_graph": bool(args.cuda_graph),
+                   "timing": "CUDA events on the compute stream around exactly K steps, device-side + host barrier "
+                             "and synchronize on both sides, max over ranks",
+                   "process_group": "gloo (bootstrap and host barriers only; no NCCL communicator)",
                    "l2": f"inputs rotate over a {pool_n}-batch device pool ({pool_n * in_bytes >> 20} MiB > 126 MiB L2)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
     }

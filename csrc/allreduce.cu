@@ -35,6 +35,8 @@
 // in the same kernel -- straight from registers in the one-shot variant.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "sgd_math.cuh"
 
 namespace {
@@ -475,6 +477,26 @@ extern "C" int dlb_barrier(void* const* sigs, uint32_t* state, int rank, int nra
     return launch(barrier_kernel, dim3(nblocks), 32, (cudaStream_t)stream, a, false);
 }
 
+// One-shot outputs in the emulation follow dlb_allreduce_oneshot's rules: 16-byte stores, and nobody
+// may write memory that a peer is still reading or writing.
+static int check_emulated_outs(void* const* bufs, void* const* outs, bool has_sgd, int nranks) {
+    DLB_REQUIRE(outs != nullptr || has_sgd, DLB_E_ARG, "dlb_allreduce_emulated: one-shot needs outs or sgds");
+    for (int r = 0; r < nranks; ++r) {
+        void* o = outs ? outs[r] : nullptr;
+        if (o == nullptr) {
+            DLB_REQUIRE(has_sgd, DLB_E_ARG, "dlb_allreduce_emulated: rank %d has neither an output nor a fused update", r);
+            continue;
+        }
+        DLB_REQUIRE((reinterpret_cast<uintptr_t>(o) & 15) == 0, DLB_E_ARG,
+                    "dlb_allreduce_emulated: output of rank %d is not 16-byte aligned", r);
+        for (int q = 0; q < nranks; ++q) {
+            DLB_REQUIRE(o != bufs[q], DLB_E_ARG, "dlb_allreduce_emulated: output of rank %d aliases the input buffer of rank %d", r, q);
+            DLB_REQUIRE(q >= r || o != outs[q], DLB_E_ARG, "dlb_allreduce_emulated: ranks %d and %d share an output buffer", q, r);
+        }
+    }
+    return 0;
+}
+
 extern "C" size_t dlb_emulated_flags_bytes(int nranks) {
     return (size_t)nranks * (DLB_SIGNAL_BYTES + 4 * DLB_STATE_WORDS);
 }
@@ -498,7 +520,8 @@ extern "C" int dlb_allreduce_emulated(int algo, void* const* bufs, void* const* 
         for (int r = 0; r < nranks; ++r) a.sgd[r] = sgds[r];
     }
     if (algo == 1) {
-        DLB_REQUIRE(outs != nullptr || sgds != nullptr, DLB_E_ARG, "dlb_allreduce_emulated: one-shot needs outs or sgds");
+        rc = check_emulated_outs(bufs, outs, sgds != nullptr, nranks);
+        if (rc) return rc;
         for (int r = 0; r < nranks; ++r) a.out[r] = outs ? outs[r] : nullptr;
         a.end_barrier = 1;
     }
@@ -540,8 +563,10 @@ constexpr size_t kStaticFlagsBytes = (size_t)DLB_MAX_RANKS * (DLB_SIGNAL_BYTES +
 static __device__ __align__(256) unsigned char g_static_flags[kStaticFlagsBytes];
 
 constexpr int kMaxDevices = 64;
-void* g_static_flags_ptr[kMaxDevices] = {};  // device address of g_static_flags, per device; host-side cache
-bool g_static_flags_ready[kMaxDevices] = {};
+// device address of g_static_flags, per device; host-side cache.  Written once per device and read by
+// any thread afterwards: an atomic pointer, so two threads making their first call on a device at
+// the same moment both look the address up (same answer) instead of racing on a plain flag.
+std::atomic<void*> g_static_flags_ptr[kMaxDevices];
 
 // In host code `g_static_flags` names a host-side shadow of the symbol, not device memory: the
 // address a kernel can use has to be asked for, once per device, with that device current.
@@ -549,14 +574,13 @@ int static_flags_for_current_device(void** out) {
     int dev = -1;
     DLB_CUDA(cudaGetDevice(&dev));
     DLB_REQUIRE(dev >= 0 && dev < kMaxDevices, DLB_E_LIMIT, "dlb_allreduce_emulated_static: device ordinal %d beyond %d", dev, kMaxDevices - 1);
-    if (!g_static_flags_ready[dev]) {
-        void* p = nullptr;
+    void* p = g_static_flags_ptr[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
         DLB_CUDA(cudaGetSymbolAddress(&p, g_static_flags));
         DLB_REQUIRE(p != nullptr, DLB_E_UNSUPPORTED, "dlb_allreduce_emulated_static: no device address for the scratch array");
-        g_static_flags_ptr[dev] = p;
-        g_static_flags_ready[dev] = true;
+        g_static_flags_ptr[dev].store(p, std::memory_order_release);
     }
-    *out = g_static_flags_ptr[dev];
+    *out = p;
     return 0;
 }
 
@@ -573,6 +597,21 @@ extern "C" int dlb_allreduce_emulated_static(int algo, void* const* bufs, void* 
     DLB_REQUIRE(nblocks >= 1 && nblocks <= DLB_MAX_BLOCKS, DLB_E_LIMIT,
                 "dlb_allreduce_emulated_static: %d CTAs per rank, the built-in scratch holds at most %d", nblocks, DLB_MAX_BLOCKS);
     DLB_REQUIRE(algo == 0 || outs != nullptr, DLB_E_ARG, "dlb_allreduce_emulated_static: one-shot needs outs");
+    // everything dlb_allreduce_emulated would refuse is refused here first, so a bad call enqueues
+    // nothing at all (not even the clearing of the scratch)
+    DLB_REQUIRE(nthreads >= 32 && nthreads <= 512 && nthreads % 32 == 0, DLB_E_ARG,
+                "dlb_allreduce_emulated_static: nthreads %d (32..512, multiple of 32)", nthreads);
+    DLB_REQUIRE(dtype == DLB_F32 || dtype == DLB_BF16, DLB_E_ARG, "dlb_allreduce_emulated_static: dtype must be fp32 or bf16");
+    DLB_REQUIRE(numel >= 0 && numel % (16 / dlb_dtype_size(dtype)) == 0, DLB_E_ARG,
+                "dlb_allreduce_emulated_static: numel %lld is not a multiple of 16 bytes' worth", (long long)numel);
+    for (int r = 0; r < nranks; ++r)
+        DLB_REQUIRE(bufs[r] != nullptr && (reinterpret_cast<uintptr_t>(bufs[r]) & 15) == 0, DLB_E_ARG,
+                    "dlb_allreduce_emulated_static: buffer of rank %d is null or not 16-byte aligned", r);
+    if (algo == 1) {
+        int orc = check_emulated_outs(bufs, outs, false, nranks);
+        if (orc) return orc;
+    }
+    if (numel == 0) return 0;
     void* flags = nullptr;
     int rc = static_flags_for_current_device(&flags);
     if (rc) return rc;

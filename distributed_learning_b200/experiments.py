@@ -134,7 +134,7 @@ def _native_factory(overlap: bool, algo: str, config):
     return functools.partial(
         B200Dist, overlap=overlap, algo=algo if config.algo == "auto" else config.algo,
         fused_sgd=bool(config.fused_sgd), comm_dtype=config.comm_dtype, model_dtype=config.dtype,
-        cuda_graph=bool(getattr(config, "cuda_graph", 0)))
+        cuda_graph=bool(getattr(config, "cuda_graph", 0)), dynamic_unused=bool(getattr(config, "dynamic_unused", 0)))
 
 
 def _immediate(fn):
@@ -149,6 +149,8 @@ def _run(config, name: str, wrapper, algo: str, two_step: bool, overlap: bool = 
         config.make_reducer = None
         _run_device(config)
         return
+    if getattr(config, "dynamic_unused", 0) and wrapper in (OurDist, SeqMergeDist):
+        wrapper = functools.partial(wrapper, dynamic_unused=True)
     config.distribute_model = wrapper
     if _device_backend(config):                      # nccl baseline, one process per GPU
         fn = {"ring": ring_allreduce_gpu, "central": central_allreduce}[algo]
@@ -230,7 +232,7 @@ def main_ddp(config):
     config.experiment_name = "ddp"
     config.make_reducer = None
     # on the native backend main_ddp stays what it is in the reference's suites: the library
-    # baseline.  The worker-level group carries NCCL for CUDA tensors, so torch DDP runs as is.
+    # baseline (it creates an NCCL sub-group for itself; the b200 job's own group is gloo only).
     if _device_backend(config):
         config.distribute_model = _ddp_cuda
         _run_device(config)
@@ -239,9 +241,21 @@ def main_ddp(config):
     worker_process(config.rank, 0, config, _NullReducer())
 
 
+_NCCL_SUBGROUP = None
+
+
 def _ddp_cuda(model, reducer, grouping_size, grad_buff_device="cpu"):
+    import torch.distributed as dist
+
+    global _NCCL_SUBGROUP
     dev = next(model.parameters()).device
-    return DDPDist(model, reducer, grouping_size, grad_buff_device, device_ids=[dev.index])
+    pg = None
+    if "nccl" not in str(dist.get_backend()):
+        # a b200 job has a gloo-only group; the library baseline brings its own NCCL communicator
+        if _NCCL_SUBGROUP is None:
+            _NCCL_SUBGROUP = dist.new_group(backend="nccl")
+        pg = _NCCL_SUBGROUP
+    return DDPDist(model, reducer, grouping_size, grad_buff_device, device_ids=[dev.index], process_group=pg)
 
 
 @experiment

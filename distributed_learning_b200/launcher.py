@@ -11,9 +11,10 @@ Differences:
 * the port can be overridden (``--master_port`` or ``$MASTER_PORT``; Q17), so two jobs can
   share a host and ``torchrun``'s port is honoured;
 * the device backends (``nccl``, ``b200``) run one process per GPU.  With ``d == 1`` the node
-  group is that group (initialised as ``cpu:gloo,cuda:nccl``: gloo carries the bootstrap and
-  handle exchange, nccl exists for the baseline).  With ``d > 1`` each spawned worker joins a
-  second, worker-level group of ``D`` ranks on ``port + 1`` (``init_worker_group``);
+  group is that group: ``cpu:gloo,cuda:nccl`` for the ``nccl`` baseline, plain ``gloo`` for ``b200``
+  (bootstrap, handle exchange and host barriers; no NCCL communicator exists on the product path).
+  With ``d > 1`` each spawned worker joins a second, worker-level group of ``D`` ranks on
+  ``port + 1`` (``init_worker_group``);
 * on the ``b200`` backend bring-up ends with GPU/NVLink *topology discovery* instead of a NIC
   name: peer-access matrix, NVLink link states and multicast capability are queried and
   logged (``distributed_learning_b200.parallel.topology``);
@@ -40,10 +41,12 @@ def master_port(config) -> int:
 
 
 def _group_backend(config, one_process_per_gpu: bool) -> str:
-    if config.backend in ("nccl", "b200") and config.use_gpu == 1 and one_process_per_gpu:
-        return "cpu:gloo,cuda:nccl"
     if config.backend == "b200":
+        # bootstrap, handle exchange and host barriers only: the product path never creates an NCCL
+        # communicator (main_ddp inside a b200 suite makes its own NCCL sub-group when it runs)
         return "gloo"
+    if config.backend == "nccl" and config.use_gpu == 1 and one_process_per_gpu:
+        return "cpu:gloo,cuda:nccl"
     return config.backend if config.backend != "nccl" or config.use_gpu == 1 else "gloo"
 
 

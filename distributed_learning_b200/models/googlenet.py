@@ -5,7 +5,7 @@ Parity: reference ``src/network.py:33-54`` wraps ``torch.hub.load('pytorch/visio
 (SURVEY.md Q15), and returns ``log_softmax(output[0])`` -- the main logits; the two
 auxiliary heads are computed in training mode and discarded.  This module builds the same
 architecture with the same parameter names, shapes and order as torchvision's
-(187 tensors, 13 004 888 parameters; ``tests/test_models.py`` checks this against torchvision
+(187 tensors, 13 004 888 parameters; ``tests/test_core_cpu.py`` checks this against torchvision
 when it is importable), and ``GoogLeNet.forward`` returns the same quantity.
 
 The 14 tensors of ``aux1``/``aux2`` (6 379 984 parameters, 49 % of the gradient bytes) never

@@ -1,7 +1,7 @@
 """ctypes loader for ``libdlb200.so`` (C ABI in ``include/dlb200.h``).
 
 The library is built in-tree by ``ops/build.py``.  ``lib()`` loads it once; when it is missing
-and nvcc is present it is built first.  There is no silent fallback: on a machine with a GPU a
+or older than the sources under ``csrc/`` and ``include/`` it is (re)built first.  There is no silent fallback: on a machine with a GPU a
 missing library is an error, because a training run that quietly used PyTorch ops instead of the
 kernels would measure the wrong thing.
 """
@@ -94,6 +94,8 @@ _PROTOS = {
     "dlb_allreduce_emulated": (c_int, [c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(FusedSgd), c_void_p, c_int,
                                        c_int64, c_int, c_float, c_int, c_int, c_void_p]),
     "dlb_emulated_flags_bytes": (c_size_t, [c_int]),
+    "dlb_host_fill_uniform": (c_int, [c_void_p, c_int, c_int64, c_uint64, c_uint64, c_int]),
+    "dlb_host_fill_randint": (c_int, [c_void_p, c_int64, c_int64, c_uint64, c_uint64]),
 }
 
 
@@ -107,13 +109,18 @@ def lib() -> ctypes.CDLL:
     if _LIB is not None:
         return _LIB
     path = library_path()
-    if not os.path.exists(path):
+    if path == _build.LIB_PATH and not _build.is_current():
+        # missing, or older than csrc/ / include/: never load a stale library silently
         try:
             _build.build_library()
         except Exception as e:  # noqa: BLE001
-            raise RuntimeError(
-                f"{path} is missing and could not be built ({e}). Run `python -m distributed_learning_b200.ops.build`."
-            ) from e
+            if not os.path.exists(path):
+                raise RuntimeError(
+                    f"{path} is missing and could not be built ({e}). Run `python -m distributed_learning_b200.ops.build`."
+                ) from e
+            import warnings
+
+            warnings.warn(f"{path} is older than its sources and could not be rebuilt ({e}); loading it as it is")
     handle = ctypes.CDLL(path)
     for name, (restype, argtypes) in _PROTOS.items():
         try:

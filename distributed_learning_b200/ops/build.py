@@ -22,7 +22,7 @@ INCLUDE = os.path.join(ROOT, "include")
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libdlb200.so")
 STAMP_PATH = LIB_PATH + ".stamp"
 
-SOURCES = ["runtime.cpp", "pack.cu", "sgd.cu", "allreduce.cu"]
+SOURCES = ["runtime.cpp", "hostgen.cpp", "pack.cu", "sgd.cu", "allreduce.cu"]
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 
@@ -60,9 +60,25 @@ def build_library(force: bool = False, verbose: bool = False, extra_flags: Optio
     """Compile every source under ``csrc/`` into ``ops/libdlb200.so``; returns its path."""
     if not force and is_current():
         return LIB_PATH
-    objdir = os.path.join(ROOT, "build", "obj")
-    os.makedirs(objdir, exist_ok=True)
     nvcc = nvcc_path()
+    os.makedirs(os.path.join(ROOT, "build"), exist_ok=True)
+    # several ranks may find the library stale at the same moment: one builds, the others wait on
+    # the lock and then see a current library
+    import fcntl
+
+    with open(os.path.join(ROOT, "build", ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_current():
+                return LIB_PATH
+            return _build_locked(nvcc, verbose, extra_flags)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(nvcc: str, verbose: bool, extra_flags: Optional[List[str]]) -> str:
+    objdir = os.path.join(ROOT, "build", f"obj.{os.getpid()}")
+    os.makedirs(objdir, exist_ok=True)
     common = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-I", INCLUDE] + ARCH_FLAGS
     if verbose:
         common += ["-Xptxas", "-v"]
@@ -90,6 +106,7 @@ def build_library(force: bool = False, verbose: bool = False, extra_flags: Optio
     os.replace(tmp, LIB_PATH)
     with open(STAMP_PATH, "w") as f:
         f.write(_fingerprint())
+    shutil.rmtree(objdir, ignore_errors=True)
     return LIB_PATH
 
 

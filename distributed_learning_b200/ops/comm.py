@@ -60,6 +60,10 @@ def default_nblocks(nbytes: int, algo: str) -> int:
     return 48
 
 
+class _ModeFailed(RuntimeError):
+    """An arena mode (vmm / ipc) failed on at least one rank; raised on every rank at the same vote."""
+
+
 class NativeComm:
     def __init__(self, group=None, device=None, prefer: str = "auto", nthreads: int = 512):
         import torch.distributed as dist
@@ -86,6 +90,7 @@ class NativeComm:
         self._handles: dict = {}
         self.tuned: Dict[Tuple[int, int], Tuple[str, int]] = {}     # (dtype code, pow2 bytes) -> (algo, nblocks)
         self.launches = 0
+        self.topology: Optional[dict] = None
 
     # ---------------------------------------------------------------------------------------
     # bring-up
@@ -99,32 +104,65 @@ class NativeComm:
         if self.world > 1:
             self._dist.barrier(group=self.group)
 
+    def _agree(self, ok: bool, what: str, exc: Optional[BaseException] = None) -> None:
+        """Collective vote after a local step.  Either every rank goes on, or every rank raises
+        ``_ModeFailed`` here -- nobody is left alone inside the next collective phase."""
+        oks = self._gather(bool(ok)) if self.world > 1 else [bool(ok)]
+        if not all(oks):
+            bad = [i for i, o in enumerate(oks) if not o]
+            raise _ModeFailed(f"{what} failed on rank(s) {bad}" + (f" (here: {exc})" if exc is not None else ""))
+
+    def _check_topology(self) -> None:
+        """Topology gate: the kernels address every peer directly, so every pair of the job's GPUs
+        must be able to map each other's memory.  A GPU with fewer active NVLink links than its
+        peers still works, at that GPU's bandwidth: warn."""
+        from ..parallel.topology import all_to_all_capable, query_topology
+        from ..utils.logging import Level, print_d
+
+        try:
+            topo = query_topology()
+        except Exception as e:  # noqa: BLE001 - discovery is advisory when the query itself fails
+            print_d(f"topology query failed ({e}); continuing without the peer-access gate", Level.WARNING)
+            topo = None
+        devs = self._gather(self.device.index) if self.world > 1 else [self.device.index]
+        self.topology = topo
+        if topo is None or self.world == 1:
+            return
+        capable = all_to_all_capable(topo, devs)
+        if not all(self._gather(capable)):
+            rows = "\n".join("  " + " ".join(str(int(x)) for x in row) for row in topo.get("peer_access", []))
+            raise RuntimeError(f"the native backend needs peer access between all of GPUs {devs}; "
+                               f"cudaDeviceCanAccessPeer matrix:\n{rows}")
+        links = {d["index"]: d.get("nvlinks_active", -1) for d in topo.get("devices", [])}
+        mine = [links.get(i, -1) for i in devs]
+        known = [x for x in mine if x >= 0]
+        if known and min(known) < max(known) and self.rank == 0:
+            print_d(f"degraded NVLink: active links per GPU {dict(zip(devs, mine))}; collectives run at the "
+                    "bandwidth of the slowest GPU", Level.WARNING)
+        ranks_perf = topo.get("performance_rank")
+        if ranks_perf and self.rank == 0:
+            worst = max(ranks_perf[a][b] for a in devs for b in devs if a != b)
+            if worst > 0:
+                print_d(f"some GPU pairs are not on the best link class (performance rank up to {worst})", Level.WARNING)
+
     def allocate(self, data_bytes: int) -> None:
         """Collective.  Allocates signal pad + ``data_bytes`` and maps all peers."""
         if self.mode is not None:
             raise RuntimeError("arena already allocated")
         total = self.data_offset + _round_up(max(data_bytes, 16), _ALIGN)
         torch.cuda.set_device(self.device)
+        self._check_topology()
         modes = {"auto": ("vmm", "ipc"), "vmm": ("vmm",), "ipc": ("ipc",)}[self.prefer]
         err: Optional[Exception] = None
         for mode in modes:
             try:
-                ok_local, exc = True, None
-                try:
-                    if mode == "vmm":
-                        self._allocate_vmm(total)
-                    else:
-                        self._allocate_ipc(total)
-                except (DlbError, OSError, RuntimeError) as e:   # noqa: PERF203
-                    ok_local, exc = False, e
-                # every rank must take the same decision
-                oks = self._gather(ok_local) if self.world > 1 else [ok_local]
-                if all(oks):
-                    self.mode = mode
-                    break
-                err = exc or RuntimeError(f"arena mode {mode} failed on ranks {[i for i, o in enumerate(oks) if not o]}")
-                self._release_partial()
-            except Exception as e:  # noqa: BLE001
+                if mode == "vmm":
+                    self._allocate_vmm(total)
+                else:
+                    self._allocate_ipc(total)
+                self.mode = mode
+                break
+            except _ModeFailed as e:         # raised on every rank at the same vote
                 err = e
                 self._release_partial()
         if self.mode is None:
@@ -137,55 +175,82 @@ class NativeComm:
     def _allocate_ipc(self, total: int) -> None:
         L = lib()
         p = c_void_p()
-        check(L.dlb_mem_alloc(total, ctypes.byref(p)))
-        self._handles = {"ipc_local": p.value, "ipc_peers": []}
         handle = ctypes.create_string_buffer(64)
-        check(L.dlb_ipc_export(p, handle))
+        self._handles = {"ipc_peers": []}
+        ok, exc = True, None
+        try:
+            check(L.dlb_mem_alloc(total, ctypes.byref(p)))
+            self._handles["ipc_local"] = p.value
+            check(L.dlb_ipc_export(p, handle))
+        except (DlbError, OSError) as e:
+            ok, exc = False, e
+        self._agree(ok, "ipc: allocate + export", exc)
         handles = self._gather(handle.raw) if self.world > 1 else [handle.raw]
         ptrs = []
-        for r, h in enumerate(handles):
-            if r == self.rank:
-                ptrs.append(p.value)
-            else:
-                q = c_void_p()
-                check(L.dlb_ipc_open(ctypes.create_string_buffer(h, 64), ctypes.byref(q)))
-                self._handles["ipc_peers"].append(q.value)
-                ptrs.append(q.value)
+        try:
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    ptrs.append(p.value)
+                else:
+                    q = c_void_p()
+                    check(L.dlb_ipc_open(ctypes.create_string_buffer(h, 64), ctypes.byref(q)))
+                    self._handles["ipc_peers"].append(q.value)
+                    ptrs.append(q.value)
+        except (DlbError, OSError) as e:
+            ok, exc = False, e
+        self._agree(ok, "ipc: open peer handles", exc)
         self.peer_ptrs = ptrs
 
     def _allocate_vmm(self, total: int) -> None:
         L = lib()
         dev = self.device.index
         h, p, rounded = c_uint64(), c_void_p(), c_size_t()
-        check(L.dlb_vmm_alloc(dev, total, ctypes.byref(h), ctypes.byref(p), ctypes.byref(rounded)))
-        self._handles = {"vmm_local": (h.value, p.value, rounded.value), "vmm_peers": []}
+        self._handles = {"vmm_peers": []}
         ptrs = [None] * self.world
-        ptrs[self.rank] = p.value
-        if self.world > 1:
-            token = self._gather(uuid.uuid4().hex if self.rank == 0 else None)[0]
-            name = lambda r: f"dlb200-{token}-{r}".encode()     # noqa: E731
-            lfd = c_int()
-            check(L.dlb_fd_listen(name(self.rank), ctypes.byref(lfd)))
-            try:
-                self._barrier()                                  # everyone is listening
-                fd = c_int()
-                check(L.dlb_vmm_export_fd(h.value, ctypes.byref(fd)))
-                for r in range(self.world):
-                    if r != self.rank:
-                        check(L.dlb_fd_send(name(r), fd.value, self.rank, 30000))
-                L.dlb_fd_close(fd.value)
-                for _ in range(self.world - 1):
-                    pfd, tag = c_int(), c_int()
-                    check(L.dlb_fd_accept(lfd.value, ctypes.byref(pfd), ctypes.byref(tag), 30000))
-                    ph, pp = c_uint64(), c_void_p()
-                    check(L.dlb_vmm_import_fd(pfd.value, ctypes.byref(ph)))
-                    L.dlb_fd_close(pfd.value)
-                    check(L.dlb_vmm_map(dev, ph.value, rounded.value, ctypes.byref(pp)))
-                    self._handles["vmm_peers"].append((ph.value, pp.value, rounded.value))
-                    ptrs[tag.value] = pp.value
-                self._barrier()
+        lfd = c_int(-1)
+        # the token is exchanged before anything can fail locally, so the vote below is the first
+        # collective a failing rank can miss -- and it does not miss it
+        token = self._gather(uuid.uuid4().hex if self.rank == 0 else None)[0] if self.world > 1 else ""
+        name = lambda r: f"dlb200-{token}-{r}".encode()     # noqa: E731
+        ok, exc = True, None
+        try:
+            check(L.dlb_vmm_alloc(dev, total, ctypes.byref(h), ctypes.byref(p), ctypes.byref(rounded)))
+            self._handles["vmm_local"] = (h.value, p.value, rounded.value)
+            ptrs[self.rank] = p.value
+            if self.world > 1:
+                check(L.dlb_fd_listen(name(self.rank), ctypes.byref(lfd)))
+        except (DlbError, OSError) as e:
+            ok, exc = False, e
+        try:
+            self._agree(ok, "vmm: allocate + listen", exc)       # doubles as "everyone is listening"
+            if self.world > 1:
+                try:
+                    fd = c_int()
+                    check(L.dlb_vmm_export_fd(h.value, ctypes.byref(fd)))
+                    try:
+                        for r in range(self.world):
+                            if r != self.rank:
+                                check(L.dlb_fd_send(name(r), fd.value, self.rank, 30000))
+                    finally:
+                        L.dlb_fd_close(fd.value)
+                    for _ in range(self.world - 1):
+                        pfd, tag = c_int(), c_int()
+                        check(L.dlb_fd_accept(lfd.value, ctypes.byref(pfd), ctypes.byref(tag), 30000))
+                        ph, pp = c_uint64(), c_void_p()
+                        try:
+                            check(L.dlb_vmm_import_fd(pfd.value, ctypes.byref(ph)))
+                        finally:
+                            L.dlb_fd_close(pfd.value)
+                        self._handles["vmm_peers"].append((ph.value, None, rounded.value))
+                        check(L.dlb_vmm_map(dev, ph.value, rounded.value, ctypes.byref(pp)))
+                        self._handles["vmm_peers"][-1] = (ph.value, pp.value, rounded.value)
+                        ptrs[tag.value] = pp.value
+                except (DlbError, OSError) as e:
+                    ok, exc = False, e
+                self._agree(ok, "vmm: exchange + map peer handles", exc)
                 self._setup_multicast(L, dev, lfd.value, name, h.value, rounded.value)
-            finally:
+        finally:
+            if lfd.value >= 0:
                 L.dlb_fd_close(lfd.value)
         self.peer_ptrs = ptrs
 
@@ -239,6 +304,26 @@ class NativeComm:
             self._handles["mc"] = (mc.value, mp.value, rounded)
 
     def _release_partial(self) -> None:
+        """Give back whatever a failed mode created (best effort: the mode is being abandoned)."""
+        L = lib()
+        h = self._handles
+        if "mc" in h:
+            mc, mp, size = h["mc"]
+            L.dlb_vmm_unmap(mp, size)
+            L.dlb_vmm_release(mc)
+        for ph, pp, size in h.get("vmm_peers", []):
+            if pp is not None:
+                L.dlb_vmm_unmap(pp, size)
+            L.dlb_vmm_release(ph)
+        if "vmm_local" in h:
+            lh, lp, size = h["vmm_local"]
+            L.dlb_vmm_unmap(lp, size)
+            L.dlb_vmm_release(lh)
+        for q in h.get("ipc_peers", []):
+            L.dlb_ipc_close(q)
+        self._barrier()                       # every rank is here (same vote): peers have let go of our block
+        if h.get("ipc_local"):
+            L.dlb_mem_free(h["ipc_local"])
         self.peer_ptrs, self.mc_ptr, self._handles = [], None, {}
 
     @property

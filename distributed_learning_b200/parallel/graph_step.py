@@ -8,6 +8,10 @@ the side stream, which joins the capture through its events, and the cross-GPU b
 epoch counters in device memory -- so the entire step can be captured once and replayed with one
 launch.  Replays run no Python, no hooks and no allocator.
 
+The constructor runs ``warmup`` eager steps and the capture on the example batch and then restores
+parameters, momentum, module buffers, step count and RNG state, so constructing the object changes
+nothing: N calls make exactly N updates, as in eager mode (``tests/test_graph_parity_gpu.py``).
+
 Constraints (checked or documented): static shapes; the learning rate and momentum are baked
 into the captured kernels (re-capture after changing them); the wrapper must be built with
 ``cuda_graph=True`` so every step uses the same arena regions and the one-shot variant keeps its
@@ -33,7 +37,14 @@ class GraphedTrainStep:
         self.loss: Optional[torch.Tensor] = None
         self.launches_per_step = 0
         dev = self.data.device
-        # eager warm-up on a side stream: builds the buckets, tunes, lets cuDNN pick algorithms
+        # The warm-up steps are real steps (they build the buckets, tune, let cuDNN pick algorithms)
+        # and must leave no trace: parameters, momentum, BatchNorm statistics, the optimizer's step
+        # count and the RNG are put back afterwards, so the first replay is the first update.
+        snap = None
+        if hasattr(wrapper, "snapshot_state"):
+            wrapper.build_now(self.data)
+            torch.cuda.synchronize(dev)
+            snap = wrapper.snapshot_state()
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
@@ -46,6 +57,10 @@ class GraphedTrainStep:
         with torch.cuda.graph(self.graph):
             self.loss = self._eager()
         self.launches_per_step = getattr(wrapper, "kernel_launches", 0) - before
+        if snap is not None:
+            torch.cuda.synchronize(dev)
+            wrapper.restore_state(snap)
+            torch.cuda.synchronize(dev)
 
     def _eager(self) -> torch.Tensor:
         self.optimizer.zero_grad()
@@ -63,6 +78,8 @@ class GraphedTrainStep:
         if target.data_ptr() != self.target.data_ptr():
             self.target.copy_(target, non_blocking=True)
         self.graph.replay()
+        if hasattr(self.optimizer, "steps"):
+            self.optimizer.steps += 1           # the replay ran the update; no Python optimizer code did
         if hasattr(self.wrapper, "kernel_launches"):
             self.wrapper.__dict__["kernel_launches"] = self.wrapper.kernel_launches + self.launches_per_step
         return self.loss

@@ -30,6 +30,7 @@ predecessors, so every rank issues the same sequence of communication kernels.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional
 
 import torch
@@ -79,14 +80,21 @@ class B200Dist(_Wrapper):
     def __init__(self, model, reducer=None, grouping_size: int = 25 * 1024 * 1024, grad_buff_device=None, *,
                  overlap: bool = True, algo: str = "auto", fused_sgd: bool = True, comm_dtype: str = "auto",
                  model_dtype: str = "fp32", cuda_graph: bool = False, group=None, comm: Optional[NativeComm] = None,
-                 exclude_unused: bool = True, unpack: str = "view", tune: bool = False):
+                 exclude_unused: bool = True, unpack: str = "view", tune: bool = False, dynamic_unused: bool = False):
         super().__init__(model, reducer)
         d = self.__dict__
         d["grouping_size"] = int(grouping_size)
         d["overlap"] = bool(overlap)
         d["algo"] = algo
         d["fused_sgd"] = bool(fused_sgd)
-        d["exclude_unused"] = exclude_unused
+        # dynamic_unused: the reference's behaviour (src/ourdist.py:137-172) -- walk the graph after
+        # EVERY forward and hand a zero gradient to the parameters this step's loss does not reach,
+        # so a model whose used-parameter set changes between steps still trains.  Every parameter
+        # is bucketed (none is excluded), and the step cannot be captured in a CUDA graph.
+        d["dynamic_unused"] = bool(dynamic_unused)
+        if d["dynamic_unused"] and cuda_graph:
+            raise ValueError("dynamic_unused walks the autograd graph every step; it cannot be combined with cuda_graph")
+        d["exclude_unused"] = exclude_unused and not d["dynamic_unused"]
         d["unpack_mode"] = unpack                      # "view" (zero copy) | "copy" (dlb_unpack into own tensors)
         d["tune_at_start"] = tune
         d["model_dtype"] = torch.bfloat16 if model_dtype in ("bf16", torch.bfloat16) else torch.float32
@@ -110,6 +118,7 @@ class B200Dist(_Wrapper):
         d["_fp32_stash"] = None
         d["kernel_launches"] = 0
         d["static_regions"] = bool(cuda_graph)   # graph replay reuses the captured region every step
+        d["nvtx"] = bool(int(os.environ.get("DLB200_NVTX", "0")))
         if d["model_dtype"] == torch.bfloat16:
             self._convert_to_bf16()
 
@@ -295,6 +304,8 @@ class B200Dist(_Wrapper):
         """Pack + allreduce (+ SGD) of one bucket on the communication stream."""
         comm, world = self.comm, self.comm.world
         cs = self.comm_stream
+        if self.nvtx:
+            torch.cuda.nvtx.range_push(f"bucket{nb.id} {nb.algo}/{nb.nblocks} {nb.nbytes >> 10} KiB")
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream(self.device))
         cs.wait_event(ready)
@@ -339,6 +350,8 @@ class B200Dist(_Wrapper):
         nb.launched = True
         self.__dict__["_last_event"] = done
         self.__dict__["kernel_launches"] = self.kernel_launches + launches
+        if self.nvtx:
+            torch.cuda.nvtx.range_pop()
 
     def forward(self, data):
         if self.model_dtype == torch.bfloat16 and data.is_floating_point() and data.dtype != torch.bfloat16:
@@ -352,7 +365,25 @@ class B200Dist(_Wrapper):
         d["_next"] = 0
         d["_armed"] = True
         d["_last_event"] = None
-        return self.model(data)
+        out = self.model(data)
+        if self.dynamic_unused:
+            self._mark_unused_ready(out)
+        return out
+
+    def _mark_unused_ready(self, out) -> None:
+        """Per-step walk: parameters the output does not depend on count as ready with no gradient
+        (the pack writes zeros for them), so their bucket still completes and every rank launches
+        the same kernels."""
+        first = out[0] if isinstance(out, (tuple, list)) else out
+        bucketed = [t for nb in self.buckets for t in nb.tensors]
+        dead = {id(p) for p in find_unused_parameters(first, bucketed)}
+        if not dead:
+            return
+        for nb in self.buckets:
+            for t in nb.tensors:
+                if id(t) in dead:
+                    t.grad = None
+                    nb.ready += 1
 
     def sync_gradients(self) -> None:
         if self.buckets is None:
@@ -369,6 +400,50 @@ class B200Dist(_Wrapper):
             torch.cuda.current_stream(self.device).wait_event(self._last_event)
         self._held.clear()
         self.__dict__["_armed"] = False
+
+    # ------------------------------------------------------------------------------------------
+    # state snapshots (used to make the CUDA-graph warm-up free of side effects)
+    # ------------------------------------------------------------------------------------------
+    def build_now(self, data) -> None:
+        """Do the first-forward set-up (probe, buckets, arena, flat parameters) without a step."""
+        if self.model_dtype == torch.bfloat16 and data.is_floating_point() and data.dtype != torch.bfloat16:
+            data = data.to(torch.bfloat16)
+        if self.buckets is None:
+            self._build(data)
+
+    def snapshot_state(self) -> dict:
+        """Copies of everything a training step changes: flat master / momentum / shadow buffers,
+        module buffers (BatchNorm statistics), the optimizer's step count and the RNG states."""
+        if self.buckets is None:
+            raise RuntimeError("snapshot_state needs the buckets: call build_now(data) first")
+        opt = self.optimizer
+        return {
+            "buckets": [(nb.master.clone(), nb.momentum.clone(), None if nb.shadow is None else nb.shadow.clone())
+                        for nb in self.buckets],
+            "buffers": [b.detach().clone() for b in self.model.buffers()],
+            "steps": None if opt is None else opt.steps,
+            "cpu_rng": torch.get_rng_state(),
+            "cuda_rng": torch.cuda.get_rng_state(self.device),
+        }
+
+    def restore_state(self, snap: dict) -> None:
+        """In-place inverse of ``snapshot_state`` (addresses are unchanged, so a captured graph stays valid)."""
+        with torch.no_grad():
+            for nb, (master, mom, shadow) in zip(self.buckets, snap["buckets"]):
+                nb.master.copy_(master)
+                nb.momentum.copy_(mom)
+                if shadow is not None:
+                    nb.shadow.copy_(shadow)
+                nb.sgd_done_in_kernel = False
+                nb.reduced = None
+            for b, v in zip(self.model.buffers(), snap["buffers"]):
+                b.copy_(v)
+        if self.optimizer is not None and snap["steps"] is not None:
+            self.optimizer.steps = snap["steps"]
+        torch.set_rng_state(snap["cpu_rng"])
+        torch.cuda.set_rng_state(snap["cuda_rng"], self.device)
+        for p in self.model.parameters():
+            p.grad = None
 
     def make_optimizer(self, lr: float = 0.01, momentum: float = 0.5, **kw) -> "FusedSGD":
         opt = FusedSGD(self, lr=lr, momentum=momentum, **kw)
@@ -395,6 +470,11 @@ class FusedSGD:
 
     def __init__(self, wrapper: B200Dist, lr: float = 0.01, momentum: float = 0.5, dampening: float = 0.0,
                  weight_decay: float = 0.0, nesterov: bool = False):
+        if nesterov and (momentum <= 0 or dampening != 0):
+            raise ValueError("Nesterov momentum requires a momentum and zero dampening")
+        if dampening != 0 and getattr(wrapper, "static_regions", False):
+            raise ValueError("dampening != 0 treats the first step differently (torch seeds the momentum buffer with "
+                             "the raw gradient), which a captured CUDA graph cannot do: use eager mode")
         self.wrapper = wrapper
         self.param_groups = [dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay,
                                   nesterov=nesterov, maximize=False, foreach=None, differentiable=False, fused=None)]
@@ -404,8 +484,12 @@ class FusedSGD:
         self.steps = 0
 
     def hyper(self):
+        """Kernel hyper-parameters of the coming step.  torch.optim.SGD seeds the momentum buffer with
+        the raw gradient on the first step (no dampening); with the buffer starting at zero that is
+        the ordinary update with dampening 0, so the first step is issued that way."""
         g = self.param_groups[0]
-        key = (g["lr"], g["momentum"], g["dampening"], g["weight_decay"], g["nesterov"])
+        damp = g["dampening"] if self.steps > 0 else 0.0
+        key = (g["lr"], g["momentum"], damp, g["weight_decay"], g["nesterov"])
         if key != self._hyper_key:
             self._hyper = F_ops.make_hyper(*key[:4], nesterov=key[4])
             self._hyper_key = key

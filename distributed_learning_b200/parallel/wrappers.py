@@ -58,13 +58,27 @@ class _Wrapper:
 
 
 class _BucketedWrapper(_Wrapper):
-    def __init__(self, model, reducer, grouping_size, grad_buff_device="cpu", exclude_unused: bool = True):
+    def __init__(self, model, reducer, grouping_size, grad_buff_device="cpu", exclude_unused: bool = True,
+                 dynamic_unused: bool = False):
         super().__init__(model, reducer)
         self.grouping_size = int(grouping_size)
         self.grad_buff_device = grad_buff_device
-        self.exclude_unused = exclude_unused
+        # dynamic_unused: the reference's per-iteration walk (src/ourdist.py:137-172): nothing is
+        # excluded, and after every forward the parameters this step's loss does not reach are
+        # marked ready with no gradient (fused as zeros, not as uninitialised memory: Q3)
+        self.dynamic_unused = bool(dynamic_unused)
+        self.exclude_unused = exclude_unused and not self.dynamic_unused
         self.groups: Optional[List[Bucket]] = None
         self.unused: List[torch.Tensor] = []
+
+    def _dead_this_step(self, output) -> set:
+        if not self.dynamic_unused:
+            return set()
+        bucketed = [t for b in self.groups for t in b.tensors]
+        dead = find_unused_parameters(output, bucketed)
+        for p in dead:
+            p.grad = None
+        return {id(p) for p in dead}
 
     def _build_groups(self, output: Optional[torch.Tensor]) -> None:
         params = [p for p in self.model.parameters() if p.requires_grad]
@@ -83,8 +97,9 @@ class _BucketedWrapper(_Wrapper):
 class OurDist(_BucketedWrapper):
     """Overlap of gradient reduction with backward, on fused buckets."""
 
-    def __init__(self, model, reducer, grouping_size=0, grad_buff_device="cpu", exclude_unused: bool = True):
-        super().__init__(model, reducer, grouping_size, grad_buff_device, exclude_unused)
+    def __init__(self, model, reducer, grouping_size=0, grad_buff_device="cpu", exclude_unused: bool = True,
+                 dynamic_unused: bool = False):
+        super().__init__(model, reducer, grouping_size, grad_buff_device, exclude_unused, dynamic_unused)
         self._hooks = []
         self._bucket_events: List[threading.Event] = []
         self._start_send = threading.Event()
@@ -159,9 +174,29 @@ class OurDist(_BucketedWrapper):
         self._iteration_armed = True
         self._start_send.set()
         self._start_recv.set()
+        dead = self._dead_this_step(output)
+        if dead:
+            for b in self.groups:
+                for t in b.tensors:
+                    if id(t) in dead and b.add_grad():
+                        self._bucket_events[b.bucket_id].set()
         return output
 
     def sync_gradients(self) -> None:
+        # backward has returned, so every hook that will fire has fired: a bucket that is still
+        # short will never fill (the set of used parameters changed) and the sender would wait on
+        # it forever.  Fail instead of hanging.
+        if self.groups is not None and self._iteration_armed:
+            short = [b for b in self.groups if b.ready != len(b.tensors)]
+            if short:
+                self._iteration_armed = False
+                self._shutting_down = True
+                for ev in self._bucket_events:
+                    ev.set()
+                b = short[0]
+                raise RuntimeError(
+                    f"bucket {b.bucket_id}: {b.ready}/{len(b.tensors)} gradients arrived; the set of parameters the "
+                    "loss depends on changed since the first step (use dynamic_unused=True / --dynamic_unused 1)")
         self._done.wait()
         self._iteration_armed = False
         if self._error is not None:
@@ -185,13 +220,15 @@ class OurDist(_BucketedWrapper):
 class SeqMergeDist(_BucketedWrapper):
     """Fusion without overlap: fuse, reduce and unfuse bucket by bucket after backward."""
 
-    def __init__(self, model, reducer, grouping_size, _grad_buffer_device="cpu", exclude_unused: bool = True):
-        super().__init__(model, reducer, grouping_size, _grad_buffer_device, exclude_unused)
+    def __init__(self, model, reducer, grouping_size, _grad_buffer_device="cpu", exclude_unused: bool = True,
+                 dynamic_unused: bool = False):
+        super().__init__(model, reducer, grouping_size, _grad_buffer_device, exclude_unused, dynamic_unused)
 
     def forward(self, data):
         output = self.model(data)
         if self.groups is None:
             self._build_groups(output)
+        self._dead_this_step(output)         # clears stale gradients of parameters unused this step
         return output
 
     def sync_gradients(self) -> None:
@@ -243,13 +280,13 @@ class DDPDist(_Wrapper):
     """torch ``DistributedDataParallel`` behind the wrapper surface (reference ``main_ddp``)."""
 
     def __init__(self, model, reducer=None, grouping_size=25 * 1024 * 1024, _grad_buffer_device="cpu",
-                 device_ids=None, find_unused_parameters: bool = True):
+                 device_ids=None, find_unused_parameters: bool = True, process_group=None):
         from torch.nn.parallel import DistributedDataParallel as DDP
 
         super().__init__(model, reducer)
         bucket_mb = max(grouping_size, 1) / 1024 / 1024
         self.__dict__["ddp"] = DDP(model, device_ids=device_ids, bucket_cap_mb=bucket_mb,
-                                   find_unused_parameters=find_unused_parameters)
+                                   find_unused_parameters=find_unused_parameters, process_group=process_group)
 
     def forward(self, data):
         return self.ddp(data)

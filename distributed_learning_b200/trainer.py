@@ -14,8 +14,9 @@ Differences, all from SURVEY.md §2.8/§7.4:
   ``f"{loss}"`` synchronise is most of the step); losses stay on the device and the loss file
   is written at the end.  ``--sync_loss 1`` restores the per-batch read-back;
 * ``--random_input 1`` generates batches on the device (K13); ``2`` reproduces the
-  reference's host RNG + copy; ``3`` is a pinned-host pool fed through ``PinnedPrefetcher``
-  (the end-to-end input path);
+  reference's host RNG + copy; ``3`` feeds the same host RNG through ``PinnedPrefetcher``
+  (pinned staging, copy one step ahead); ``4`` replaces the host RNG by the native
+  multi-threaded generator writing the pinned slot (the end-to-end input path of ``bench.py``);
 * the wrapper may provide its own optimizer (``make_optimizer``: the fused SGD kernel);
 * checkpoint/resume (``--checkpoint``, ``--checkpoint_every``, ``--resume``);
 * initial weights are broadcast from rank 0 when a process group exists (Q13).
@@ -34,7 +35,7 @@ import torch.optim as optim
 
 from .utils.checkpoint import load_checkpoint, save_checkpoint
 from .utils.config import picklable_config
-from .utils.data import PinnedPrefetcher, random_data_generator
+from .utils.data import NativeHostRandom, PinnedPrefetcher, random_data_generator
 from .utils.logging import Level, print_d
 from .utils.timing import PhaseTimer
 
@@ -116,7 +117,9 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
         batch_count, start_epoch = payload["batch_count"], payload["epoch"]
         print_d(f"Resumed from {ckpt} at batch {batch_count}", Level.INFO)
 
-    timer = PhaseTimer(device, mode=getattr(config, "timer", "auto"))
+    timer = PhaseTimer(device, mode=getattr(config, "timer", "auto"), nvtx=bool(getattr(config, "nvtx", 0)))
+    if getattr(config, "nvtx", 0) and hasattr(model, "__dict__"):
+        model.__dict__["nvtx"] = True          # per-bucket ranges inside the native wrapper
     sync_loss = bool(getattr(config, "sync_loss", 0 if on_gpu else 1))
     pending_losses = []          # (batch_count, device scalar) when the loss is not read back per batch
     loss_path = f"{config.folder}/{name}_{node_id}_{worker_id}_loss.txt"
@@ -146,8 +149,12 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
                 gener = random_data_generator(first, device=device if on_gpu else None)
             elif random_input == 2:
                 gener = random_data_generator(first)
-            else:
+            elif random_input == 3:
                 gener = PinnedPrefetcher(random_data_generator(first), device,
+                                         channels_last=bool(getattr(config, "channels_last", 0)))
+            else:
+                # 4: the end-to-end input path with the native host generator (csrc/hostgen.cpp)
+                gener = PinnedPrefetcher(NativeHostRandom.like(first, seed=1234 + node_id * 64 + worker_id), device,
                                          channels_last=bool(getattr(config, "channels_last", 0)))
         while batch_count < limit:
             timer.start("batch")

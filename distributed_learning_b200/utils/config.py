@@ -73,6 +73,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--sync_loss", type=int, default=None,
                    help="read the loss back every batch like the reference (default: 1 on cpu, 0 on gpu where losses are flushed at the end)")
     p.add_argument("--seed", type=int, default=1234)
+    p.add_argument("--dynamic_unused", type=int, default=0,
+                   help="re-detect parameters without gradient after every forward, like the reference "
+                        "(default: detect once at the first step and leave them out)")
+    p.add_argument("--nvtx", type=int, default=0, help="emit NVTX ranges around the phases and the per-bucket launches")
     return p
 
 
@@ -98,10 +102,12 @@ def finalize_config(config: argparse.Namespace) -> argparse.Namespace:
         config.sync_loss = 0 if config.use_gpu == 1 else 1
     if config.backend == "b200" and config.use_gpu != 1:
         raise SystemExit("--backend b200 is the NVLink path: it needs g=1 (use --backend gloo on the CPU)")
-    if getattr(config, "cuda_graph", 0) and int(config.random_input) == 3:
+    if getattr(config, "cuda_graph", 0) and int(config.random_input) in (3, 4):
         # the prefetcher's staging thread pins host memory while the step is being captured, which
         # a global-mode capture does not allow; bench.py shows the supported order (capture first)
         raise SystemExit("--cuda_graph 1 cannot be combined with --random_input 3 in main.py; use --random_input 1 or 2")
+    if getattr(config, "cuda_graph", 0) and getattr(config, "dynamic_unused", 0):
+        raise SystemExit("--dynamic_unused 1 walks the autograd graph every step and cannot be captured: drop --cuda_graph")
     if config.backend == "b200" and config.total_dev > 8:
         raise SystemExit("--backend b200 spans one NVSwitch domain (at most 8 GPUs); use --backend nccl beyond that")
     if config.size * config.node_dev != config.total_dev:

@@ -212,6 +212,57 @@ def synthetic_batches(model_type: str, batch_size: int, device, dtype=torch.floa
                torch.randint(classes, (batch_size,), device=device))
 
 
+class NativeHostRandom:
+    """Fresh random batches made on the host by the native generator (``csrc/hostgen.cpp``).
+
+    The job is the reference's ``random_data_generator`` on the host (``src/data.py:129-132``):
+    every step a new ``(data, target)`` pair of the template's shape.  The reference draws it from
+    torch's serial host RNG; here a few threads fill the *pinned staging slot itself*
+    (``fill_into``, used by ``PinnedPrefetcher``), so a batch costs a few milliseconds and one pass
+    over memory.  Iterating the object directly yields ordinary CPU tensors instead.
+    ``dtype=torch.bfloat16`` writes bf16 on the host and halves the bytes of the H2D copy.
+    """
+
+    def __init__(self, shape, num_classes: int, seed: int = 0, dtype: torch.dtype = torch.float32,
+                 nthreads: Optional[int] = None):
+        self.shape = tuple(shape)               # (batch, C, H, W)
+        self.num_classes = int(num_classes)
+        self.seed = int(seed)
+        self.dtype = dtype
+        if nthreads is None:
+            world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", 1)))
+            nthreads = max(1, min(8, (os.cpu_count() or 1) // max(world, 1)))
+        self.nthreads = int(os.environ.get("DLB200_HOSTGEN_THREADS", nthreads))
+        self.batch_index = 0
+
+    @classmethod
+    def like(cls, data_pair, **kw) -> "NativeHostRandom":
+        data, target = data_pair
+        return cls(tuple(data.shape), int(target.max()) + 1, **kw)
+
+    def template(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        return torch.empty(self.shape, dtype=self.dtype), torch.empty(self.shape[0], dtype=torch.int64)
+
+    def fill_into(self, data: torch.Tensor, target: torch.Tensor) -> None:
+        """Overwrite ``data`` / ``target`` (CPU tensors of the template's size) with the next batch.
+        The memory format of ``data`` is irrelevant: the values are i.i.d."""
+        from ..ops._lib import check, dtype_code, lib
+
+        L = lib()
+        check(L.dlb_host_fill_uniform(data.data_ptr(), dtype_code(data.dtype), data.numel(), self.seed, self.batch_index,
+                                      self.nthreads))
+        check(L.dlb_host_fill_randint(target.data_ptr(), target.numel(), self.num_classes, self.seed, self.batch_index))
+        self.batch_index += 1
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        data, target = self.template()
+        self.fill_into(data, target)
+        return data, target
+
+
 class PinnedPrefetcher:
     """Host->device input pipeline: a staging thread, pinned buffers, and a copy stream that runs
     one step ahead of the compute stream.
@@ -230,7 +281,7 @@ class PinnedPrefetcher:
         import queue
         import threading
 
-        self.source = iter(source)
+        self.source = source if hasattr(source, "fill_into") else iter(source)
         self.device = torch.device(device)
         self.cuda = self.device.type == "cuda"
         self.depth = max(2, depth)
@@ -253,6 +304,9 @@ class PinnedPrefetcher:
     # -- staging thread ------------------------------------------------------------------------
     def _stage_loop(self):
         try:
+            if hasattr(self.source, "fill_into"):
+                self._fill_loop()
+                return
             for data, target in self.source:
                 if self._stop:
                     break
@@ -273,6 +327,23 @@ class PinnedPrefetcher:
             self._staged.put(None)
         except BaseException as e:  # noqa: BLE001 - re-raised in the consumer
             self._staged.put(e)
+
+    def _fill_loop(self):
+        """Sources that can write a batch in place (``NativeHostRandom``): no intermediate tensor,
+        the generator's threads write the pinned slot the copy engine reads."""
+        src = self.source
+        while not self._stop:
+            i = self._free.get()
+            if self._stop:
+                break
+            if self._slots[i] is None:
+                data, target = src.template()
+                fmt = torch.channels_last if (self.channels_last and data.dim() == 4) else torch.contiguous_format
+                self._slots[i] = (data.contiguous(memory_format=fmt).pin_memory(), target.pin_memory(), torch.cuda.Event())
+            hd, ht, free_ev = self._slots[i]
+            free_ev.synchronize()
+            src.fill_into(hd, ht)
+            self._staged.put((hd, ht, i))
 
     # -- consumer side ---------------------------------------------------------------------------
     def _queue_next(self):
@@ -318,6 +389,8 @@ class PinnedPrefetcher:
 
     def close(self) -> None:
         self._stop = True
+        if self.cuda:
+            self._free.put(0)          # wake a staging thread that waits for a free slot
 
 
 # ------------------------------------------------------------------------------------------

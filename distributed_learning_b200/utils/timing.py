@@ -59,8 +59,11 @@ class PhaseTimer:
     (device when ``device`` is a CUDA device).
     """
 
-    def __init__(self, device=None, mode: str = "auto"):
+    def __init__(self, device=None, mode: str = "auto", nvtx: bool = False):
         dev = torch.device(device) if device is not None else torch.device("cpu")
+        # NVTX: every phase is also a named range on the calling thread, so a profiler timeline
+        # (ncu --nvtx, nsys) shows get_data / forward / backprop / sync / optimizer_step / batch
+        self.nvtx = bool(nvtx) and dev.type == "cuda"
         if mode == "auto":
             mode = "device" if dev.type == "cuda" else "host"
         if mode not in ("host", "device"):
@@ -75,6 +78,8 @@ class PhaseTimer:
 
     # -- recording ---------------------------------------------------------------------
     def start(self, name: str) -> None:
+        if self.nvtx:
+            torch.cuda.nvtx.range_push(name)
         self._open[name] = self._span_cls()
 
     def end(self, name: str) -> None:
@@ -82,6 +87,8 @@ class PhaseTimer:
         if span is None:
             raise KeyError(f"end_timer('{name}') without start_timer('{name}')")
         span.stop()
+        if self.nvtx:
+            torch.cuda.nvtx.range_pop()
         self._step.setdefault(name, []).append(span)
 
     def end_step(self, experiment_name: str, extra_fields: Optional[dict] = None) -> None:

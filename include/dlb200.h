@@ -94,6 +94,16 @@ int dlb_mc_add_device(uint64_t mc_handle, int dev);
 int dlb_mc_bind(uint64_t mc_handle, size_t mc_offset, uint64_t mem_handle, size_t bytes);
 int dlb_mc_map(int dev, uint64_t mc_handle, size_t bytes, void** mc_ptr);
 
+/* ---- host-side synthetic input (reference random_data_generator, src/data.py:129-132) -------
+ * Fill `numel` elements at `dst` (host memory, normally the pinned slot an H2D copy will read)
+ * with uniform values in [0,1) (fp32 or bf16) or labels in [0,high).  Counter based: element i of
+ * batch `batch_index` depends only on (seed, batch_index, i), so the result is independent of
+ * `nthreads`, which only sets how many threads share the work (the call returns when all are
+ * done).  The reference draws the same data from one serial host RNG stream, 69 ms per
+ * 128x3x224x224 batch on the B200 host. */
+int dlb_host_fill_uniform(void* dst, int dtype, int64_t numel, uint64_t seed, uint64_t batch_index, int nthreads);
+int dlb_host_fill_randint(int64_t* dst, int64_t numel, int64_t high, uint64_t seed, uint64_t batch_index);
+
 /* ---- K-pack / K-unpack (reference Group.fuse / Group.unfuse, src/ourdist.py:28-43) -----------
  * One launch moves up to DLB_MAX_TENSORS tensors (longer lists: several launches) between their own storage and a flat fusion
  * buffer: flat[offset[i] + k] = cast(tensor_i[k] * scale)  (pack)  or the reverse (unpack).

@@ -255,6 +255,9 @@ def test_launcher_port_and_backend_selection(monkeypatch):
     monkeypatch.delenv("MASTER_PORT")
     assert launcher.master_port(parse_args(ARGV)) == 29501              # the reference's fixed port
     g = parse_args(["1", "0", "1", "1", "a", "i", "mnist", "/r", "1", "--backend", "b200"])
-    assert launcher._group_backend(g, one_process_per_gpu=True) == "cpu:gloo,cuda:nccl"
+    # the product backend never creates an NCCL communicator: gloo carries the bootstrap
+    assert launcher._group_backend(g, one_process_per_gpu=True) == "gloo"
     assert launcher._group_backend(g, one_process_per_gpu=False) == "gloo"
+    n = parse_args(["1", "0", "1", "1", "a", "i", "mnist", "/r", "1", "--backend", "nccl"])
+    assert launcher._group_backend(n, one_process_per_gpu=True) == "cpu:gloo,cuda:nccl"
     assert launcher._group_backend(parse_args(ARGV), True) == "gloo"

@@ -113,3 +113,76 @@ def test_b200_backend_needs_gpu_flag():
         parse_args(["1", "0", "1", "1", "a", "i", "mnist", "/r", "0", "--backend", "b200"])
     with pytest.raises(SystemExit):
         parse_args(["2", "0", "8", "16", "a", "i", "mnist", "/r", "1", "--backend", "b200"])
+
+
+# ---- a changing set of used parameters ---------------------------------------------------------------
+class _TwoHeads(torch.nn.Module):
+    """The loss reaches head `a` or head `b` depending on a flag: the used-parameter set changes."""
+
+    def __init__(self):
+        super().__init__()
+        self.body = torch.nn.Linear(6, 6)
+        self.a = torch.nn.Linear(6, 3)
+        self.b = torch.nn.Linear(6, 3)
+        self.use_b = False
+
+    def forward(self, x):
+        h = torch.relu(self.body(x))
+        return torch.log_softmax((self.b if self.use_b else self.a)(h), dim=1)
+
+
+class _LocalReducer:
+    def __init__(self):
+        import queue
+
+        self.q = queue.Queue()
+
+    def put(self, buf):
+        self.q.put(buf)
+
+    def get(self):
+        return self.q.get()
+
+    def cleanup(self):
+        pass
+
+
+def test_ourdist_raises_instead_of_hanging_when_the_used_set_changes():
+    import pytest
+
+    from distributed_learning_b200.parallel.wrappers import OurDist
+
+    torch.manual_seed(0)
+    m = _TwoHeads()
+    w = OurDist(m, _LocalReducer(), 1 << 20)
+    x = torch.rand(4, 6)
+    w(x).sum().backward()
+    w.sync_gradients()                      # first step: head b is found unused and left out
+    m.use_b = True
+    for p in m.parameters():
+        p.grad = None
+    w(x).sum().backward()                   # now head a gets no gradient: its bucket never fills
+    with pytest.raises(RuntimeError, match="set of parameters"):
+        w.sync_gradients()
+    w.cleanup()
+
+
+def test_dynamic_unused_follows_a_changing_used_set():
+    from distributed_learning_b200.parallel.wrappers import OurDist, SeqMergeDist
+
+    for cls in (OurDist, SeqMergeDist):
+        torch.manual_seed(0)
+        m = _TwoHeads()
+        w = cls(m, _LocalReducer(), 1 << 20, dynamic_unused=True)
+        x = torch.rand(4, 6)
+        for use_b in (False, True, False):
+            m.use_b = use_b
+            for p in m.parameters():
+                p.grad = None
+            w(x).sum().backward()
+            w.sync_gradients()
+            used, unused = (m.b, m.a) if use_b else (m.a, m.b)
+            assert used.weight.grad is not None and float(used.weight.grad.abs().sum()) > 0
+            assert unused.weight.grad is not None and float(unused.weight.grad.abs().sum()) == 0, \
+                "a parameter the loss did not reach gets a zero gradient, not stale or uninitialised memory"
+        w.cleanup()
