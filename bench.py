@@ -51,6 +51,7 @@ def parse_args():
     p.add_argument("--grouping-size", type=int, default=25 * 1024 * 1024)
     p.add_argument("--algo", default="auto")
     p.add_argument("--fused-sgd", type=int, default=1)
+    p.add_argument("--fuse-pack", type=int, default=1, help="gather the gradients in the allreduce kernel's prologue (one launch per bucket)")
     p.add_argument("--overlap", type=int, default=1)
     p.add_argument("--tune", type=int, default=1, help="measure the allreduce variants once and pick per bucket size")
     p.add_argument("--channels-last", type=int, default=1, help="NHWC activations/weights (layout only; same arithmetic)")

@@ -74,7 +74,7 @@ def run(args, helpers) -> dict:
     model.train()
     broadcast_initial_state(model)          # before wrapping: the wrapper re-homes the parameters
     wrapper = B200Dist(model, None, args.grouping_size, device, overlap=bool(args.overlap), algo=args.algo,
-                       fused_sgd=bool(args.fused_sgd), model_dtype=dtype, tune=bool(args.tune),
+                       fused_sgd=bool(args.fused_sgd), fuse_pack=bool(args.fuse_pack), model_dtype=dtype, tune=bool(args.tune),
                        cuda_graph=bool(args.cuda_graph))
     opt = wrapper.make_optimizer(lr=0.01, momentum=0.5)
     step = _make_step(wrapper, opt)
@@ -147,8 +147,8 @@ def run(args, helpers) -> dict:
                                      "input": "fresh batch every step generated on the device (torch.rand), loss read back"}
 
     wrapper.comm.check()
-    buckets = [{"mib": round(nb.numel * nb.regions[0].element_size() / 2**20, 2), "algo": nb.algo, "nblocks": nb.nblocks}
-               for nb in wrapper.buckets]
+    buckets = [{"mib": round(nb.numel * nb.regions[0].element_size() / 2**20, 2), "algo": nb.algo, "nblocks": nb.nblocks,
+                "unroll": nb.unroll} for nb in wrapper.buckets]
     result = {
         "metric": helpers.METRIC,
         "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -160,7 +160,7 @@ def run(args, helpers) -> dict:
                              "cifar": "basicnet-cifar"}[model_type],
                    "global_batch": bs * world, "per_gpu_batch": bs, "seq_len": None,
                    "input": list(shape), "parallelism": f"dp{world}", "optimizer": "sgd lr=0.01 momentum=0.5",
-                   "grouping_size": args.grouping_size, "buckets": buckets, "fused_sgd": bool(args.fused_sgd),
+                   "grouping_size": args.grouping_size, "buckets": buckets, "fused_sgd": bool(args.fused_sgd), "fuse_pack": bool(wrapper.fuse_pack),
                    "overlap": bool(args.overlap), "arena": wrapper.comm.mode, "multicast": wrapper.comm.has_multicast,
                    "multicast_note": wrapper.comm.mc_note,
                    "channels_last": bool(args.channels_last), "cudnn_benchmark": bool(args.cudnn_benchmark),

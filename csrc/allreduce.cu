@@ -1,11 +1,12 @@
 // allreduce.cu -- K-ar: allreduce kernels that read and write peer GPUs' fusion buffers directly
-// over NVLink 5 / NVSwitch, with the averaging scale and the SGD update fused in.
+// over NVLink 5 / NVSwitch, with the gradient pack, the averaging scale and the SGD update fused in.
 //
 // Replaces the host-driven algorithms of reference src/allreduce.py (a Python isend/recv ring
 // over gloo on CPU tensors, :45-98; a broadcast-emulated NCCL ring, :100-170; a central
-// gather/scatter, :9-43) and the intra-node host sum of src/reducers.py:59-62.  Behind NVSwitch
-// every peer is one hop away at full bandwidth, so there is no ring: every GPU talks to every
-// other GPU at once.
+// gather/scatter, :9-43), the intra-node host sum of src/reducers.py:59-62, and -- with the fused
+// prologue -- the per-tensor copies of Group.fuse (src/ourdist.py:28-36).  Behind NVSwitch every
+// peer is one hop away at full bandwidth, so there is no ring: every GPU talks to every other GPU
+// at once.
 //
 //   two-shot  rank r pulls slice r of the buffer from all N peers (16-byte loads on peer
 //             pointers), sums in fp32 in rank order, scales, and pushes the result into slice r
@@ -15,7 +16,15 @@
 //   one-shot  every rank pulls the whole buffer from all peers and reduces locally: (N-1) S
 //             inbound, one barrier; wins when the buffer is small and latency dominates.
 //   nvls      multimem.ld_reduce pulls slice r already summed by the switch, multimem.st
-//             broadcasts the result through the switch: about S/N + S per direction.
+//             broadcasts the result through the switch: about S/N + S per direction.  `unroll`
+//             (2, 4 or 8) is how many switch reductions a thread has in flight.
+//
+// One kernel per bucket.  With a tensor table (`ntensors > 0`) the kernel starts by PACKING: CTA b
+// gathers, from the gradient tensors' own storage, exactly the tiles of the local buffer that the
+// peers' CTAs number b will pull after the barrier ("column b", see below), so the entry barrier
+// doubles as "my part of the pack is visible" and no separate pack launch or grid-wide sync is
+// needed.  With `sgd` set the kernel ends by consuming the reduced gradient in the SGD-momentum
+// update -- straight from registers in the one-shot variant.
 //
 // Device-side barrier: rank r's CTA b writes an epoch number into slot [b][r] of every peer's
 // signal pad (st.release.sys after a CTA barrier) and spins (ld.acquire.sys) on its own pad's
@@ -23,21 +32,22 @@
 // barrier ahead of a peer, so one slot per (CTA, peer) is enough and nothing is ever reset.
 // The epoch counter lives in device memory, so launches can be captured in a CUDA graph.
 // A CTA only ever waits for the *same-numbered* CTA of its peers.  The work is split so that
-// this is sufficient: CTA b owns "column b" -- tiles b, b+G, b+2G... of every slice -- both
-// when it reduces slice r and when it runs the epilogue over all slices, so everything a CTA
-// consumes after a barrier was produced by the CTAs it has just synchronised with.  The waits
+// this is sufficient: CTA b owns "column b" -- tiles b, b+G, b+2G... of every slice -- when it
+// packs, when it reduces slice r and when it runs the epilogue over all slices, so everything a
+// CTA consumes after a barrier was produced by the CTAs it has just synchronised with.  The waits
 // are bounded (dlb_set_wait_timeout_ms): a missing peer sets the error word instead of hanging.
 //
 // Every CTA of every rank must be resident while it waits, so grids are small (<= 64 CTAs) and
-// all ranks must issue the same sequence of launches with the same grid.
+// all ranks must issue the same sequence of launches with the same grid, block size and unroll.
 //
-// Fused epilogue: with `sgd` set, the reduced gradient is consumed by the SGD-momentum update
-// in the same kernel -- straight from registers in the one-shot variant.
+// `trace` (optional, 8 x uint64 per rank) receives %globaltimer at the phase boundaries of CTA 0:
+// start, packed, entry barrier passed, data phase done, exit barrier passed, epilogue done.
 #include <stdlib.h>
 
 #include <atomic>
 
 #include "sgd_math.cuh"
+#include "tensor_table.cuh"
 
 namespace {
 
@@ -48,10 +58,11 @@ struct CommArgs {
     dlb_fused_sgd_t sgd[DLB_MAX_RANKS];
     uint32_t* state;  // epoch[DLB_MAX_BLOCKS] + error word (emulation: one block of DLB_STATE_WORDS per rank)
     void* mc;         // multicast mapping (nvls)
-    int64_t nvec;     // 16-byte vectors in the buffer
+    unsigned long long* trace;
+    int64_t nvec;  // 16-byte vectors in the buffer
     uint64_t timeout_ns;
-    float scale;
-    int rank, nranks, end_barrier, has_sgd;
+    float scale, pack_scale;
+    int rank, nranks, end_barrier, has_sgd, root;
 };
 
 // 10 minutes, the order of NCCL's watchdog: long enough for a rank that is still loading data or
@@ -73,6 +84,10 @@ uint64_t wait_timeout_ns() {
 template <int NR>
 __device__ __forceinline__ int ranks_of(const CommArgs& a) {
     return NR > 0 ? NR : a.nranks;
+}
+
+__device__ __forceinline__ void trace_mark(const CommArgs& a, int rank_slot, int i) {
+    if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[rank_slot * 8 + i] = global_timer_ns();
 }
 
 // ---- barrier ------------------------------------------------------------------------------------
@@ -117,42 +132,103 @@ __device__ __forceinline__ void accumulate(float* acc, const vec16& v) {
     for (int i = 0; i < VecOf<T>::N; ++i) acc[i] += f[i];
 }
 
-// The epilogue of two-shot / nvls: SGD over this CTA's column of every slice of the local buffer.
-template <typename T, int NR>
-__device__ __forceinline__ void sgd_epilogue(const CommArgs& a, const dlb_fused_sgd_t& s, const char* local,
-                                             int64_t slice, int64_t tile) {
+// ---- column walk ----------------------------------------------------------------------------------
+// CTA b's column: tiles b, b+G, ... of each of the `nr` slices.  `q` enumerates them slice-major.
+struct Column {
+    int64_t slice, tile, nvec;
+    int per_slice;  // tiles of one slice that this CTA owns
+    int count;      // per_slice * nr
+    __device__ __forceinline__ Column(int64_t nvec_, int nr, int64_t tile_) {
+        nvec = nvec_;
+        tile = tile_;
+        slice = (nvec + nr - 1) / nr;
+        const int64_t ts = (slice + tile - 1) / tile;  // tiles per slice
+        per_slice = (int)blockIdx.x < ts ? (int)((ts - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+        count = per_slice * nr;
+    }
+    // vector index of (tile q, position u*blockDim + tid), or -1 past the slice / the buffer
+    __device__ __forceinline__ int64_t vec_of(int q, int u) const {
+        const int sl = q / per_slice, i = q - sl * per_slice;
+        const int64_t within = ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * tile + (int64_t)u * blockDim.x + threadIdx.x;
+        const int64_t j = sl * slice + within;
+        return (within < slice && j < nvec) ? j : -1;
+    }
+};
+
+// The prologue: gather this CTA's column of the local buffer from the gradient tensors.
+// PU tiles x U vectors are in flight per thread.
+template <typename T, int U>
+__device__ __forceinline__ void pack_columns(const CommArgs& a, const TableSmem& s, int ntensors, char* local, int nr) {
     constexpr int N = VecOf<T>::N;
-    constexpr int U = Unroll<NR>::U;
-    const int nr = ranks_of<NR>(a);
-    for (int sl = 0; sl < nr; ++sl) {
-        const int64_t sbegin = sl * slice, send = min(sbegin + slice, a.nvec);
-        for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < slice; t0 += (int64_t)gridDim.x * tile) {
+    constexpr int PU = U >= 8 ? 1 : 8 / U;
+    const Column col(a.nvec, nr, (int64_t)blockDim.x * U);
+    Owner own;
+    for (int q0 = 0; q0 < col.count; q0 += PU) {
+        Gathered g[PU][U];
+        int64_t j[PU][U];
+#pragma unroll
+        for (int p = 0; p < PU; ++p) {
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                const int64_t j = sbegin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
-                if (j < send) {
-                    float g[N];
-                    VecOf<T>::to_float(ld_vec(local + j * 16), g);
-                    sgd_apply_vec<N>(s, (size_t)j * N, g);
+                j[p][u] = q0 + p < col.count ? col.vec_of(q0 + p, u) : -1;
+                g[p][u].kind = -1;
+                if (j[p][u] >= 0) gather_issue<T>(s, ntensors, (uint32_t)j[p][u], own, g[p][u]);
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < PU; ++p) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                float f[N];
+                if (j[p][u] >= 0 && gather_finish<T>(g[p][u], f)) {
+#pragma unroll
+                    for (int i = 0; i < N; ++i) f[i] *= a.pack_scale;
+                    st_vec(local + j[p][u] * 16, VecOf<T>::from_float(f));
                 }
             }
         }
     }
 }
 
+// The epilogue of two-shot / nvls: SGD over this CTA's column of every slice of the local buffer.
+template <typename T, int U>
+__device__ __forceinline__ void sgd_epilogue(const CommArgs& a, const dlb_fused_sgd_t& s, const char* local, int nr) {
+    constexpr int N = VecOf<T>::N;
+    const Column col(a.nvec, nr, (int64_t)blockDim.x * U);
+    for (int q = 0; q < col.count; ++q) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t j = col.vec_of(q, u);
+            if (j >= 0) {
+                float g[N];
+                VecOf<T>::to_float(ld_vec(local + j * 16), g);
+                sgd_apply_vec<N>(s, (size_t)j * N, g);
+            }
+        }
+    }
+}
+
 // ---- two-shot -------------------------------------------------------------------------------------
-template <typename T, int NR, bool EMU>
-__global__ void __launch_bounds__(512, 1) twoshot_kernel(const __grid_constant__ CommArgs a) {
+template <typename T, int NR, bool EMU, bool PACK>
+__device__ __forceinline__ void twoshot_body(const CommArgs& a, const TensorTable* tab, TableSmem* ts) {
     constexpr int N = VecOf<T>::N;
     constexpr int U = Unroll<NR>::U;
     constexpr int R = Unroll<NR>::R;
     const int nr = ranks_of<NR>(a);
     const int rank = EMU ? (int)blockIdx.y : a.rank;
+    const int slot = EMU ? rank : 0;
     uint32_t* state = a.state + (EMU ? rank * DLB_STATE_WORDS : 0);
     uint32_t* err = state + DLB_MAX_BLOCKS;
     uint32_t epoch = state[blockIdx.x];
 
+    trace_mark(a, slot, 0);
+    if (PACK) {
+        table_stage(*ts, *tab, rank);
+        pack_columns<T, U>(a, *ts, tab->ntensors, reinterpret_cast<char*>(a.buf[rank]), nr);
+    }
+    trace_mark(a, slot, 1);
     block_barrier<NR>(a, rank, ++epoch, err);  // every rank's buffer holds its packed gradients
+    trace_mark(a, slot, 2);
 
     const int64_t slice = (a.nvec + nr - 1) / nr;
     const int64_t begin = rank * slice, end = min(begin + slice, a.nvec);
@@ -186,31 +262,80 @@ __global__ void __launch_bounds__(512, 1) twoshot_kernel(const __grid_constant__
             }
         }
     }
+    trace_mark(a, slot, 3);
 
     block_barrier<NR>(a, rank, ++epoch, err);  // all slices have landed in every buffer
+    trace_mark(a, slot, 4);
 
-    if (a.has_sgd)
-        sgd_epilogue<T, NR>(a, a.sgd[EMU ? rank : 0], reinterpret_cast<const char*>(a.buf[rank]), slice, tile);
+    if (a.has_sgd) sgd_epilogue<T, U>(a, a.sgd[slot], reinterpret_cast<const char*>(a.buf[rank]), nr);
     if (threadIdx.x == 0) state[blockIdx.x] = epoch;
+    trace_mark(a, slot, 5);
+}
+
+template <typename T, int NR, bool EMU>
+__global__ void __launch_bounds__(512, 1) twoshot_kernel(const __grid_constant__ CommArgs a) {
+    twoshot_body<T, NR, EMU, false>(a, nullptr, nullptr);
+}
+template <typename T, int NR, bool EMU>
+__global__ void __launch_bounds__(512, 1) twoshot_pack_kernel(const __grid_constant__ CommArgs a,
+                                                              const __grid_constant__ TensorTable tab) {
+    __shared__ TableSmem ts;
+    twoshot_body<T, NR, EMU, true>(a, &tab, &ts);
 }
 
 // ---- one-shot -------------------------------------------------------------------------------------
-template <typename T, int NR, bool EMU>
-__global__ void __launch_bounds__(512, 1) oneshot_kernel(const __grid_constant__ CommArgs a) {
+template <typename T, int NR, bool EMU, bool PACK>
+__device__ __forceinline__ void oneshot_body(const CommArgs& a, const TensorTable* tab, TableSmem* ts) {
     constexpr int N = VecOf<T>::N;
     constexpr int U = Unroll<NR>::U;
     constexpr int R = Unroll<NR>::R;
     const int nr = ranks_of<NR>(a);
     const int rank = EMU ? (int)blockIdx.y : a.rank;
+    const int slot = EMU ? rank : 0;
     uint32_t* state = a.state + (EMU ? rank * DLB_STATE_WORDS : 0);
     uint32_t* err = state + DLB_MAX_BLOCKS;
     uint32_t epoch = state[blockIdx.x];
-    char* out = reinterpret_cast<char*>(a.out[EMU ? rank : 0]);
-    const dlb_fused_sgd_t& sgd = a.sgd[EMU ? rank : 0];
-
-    block_barrier<NR>(a, rank, ++epoch, err);
-
+    char* out = reinterpret_cast<char*>(a.out[slot]);
+    const dlb_fused_sgd_t& sgd = a.sgd[slot];
     const int64_t tile = (int64_t)blockDim.x * U;
+
+    trace_mark(a, slot, 0);
+    if (PACK) {
+        // one-shot has no slices: CTA b packs and pulls tiles b, b+G, ... of the whole buffer
+        constexpr int PU = U >= 8 ? 1 : 8 / U;
+        table_stage(*ts, *tab, rank);
+        char* local = reinterpret_cast<char*>(a.buf[rank]);
+        Owner own;
+        for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < a.nvec; t0 += (int64_t)gridDim.x * tile * PU) {
+            Gathered g[PU][U];
+#pragma unroll
+            for (int p = 0; p < PU; ++p) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int64_t j = t0 + (int64_t)p * gridDim.x * tile + (int64_t)u * blockDim.x + threadIdx.x;
+                    g[p][u].kind = -1;
+                    if (j < a.nvec) gather_issue<T>(*ts, tab->ntensors, (uint32_t)j, own, g[p][u]);
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < PU; ++p) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int64_t j = t0 + (int64_t)p * gridDim.x * tile + (int64_t)u * blockDim.x + threadIdx.x;
+                    float f[N];
+                    if (j < a.nvec && gather_finish<T>(g[p][u], f)) {
+#pragma unroll
+                        for (int i = 0; i < N; ++i) f[i] *= a.pack_scale;
+                        st_vec(local + j * 16, VecOf<T>::from_float(f));
+                    }
+                }
+            }
+        }
+    }
+    trace_mark(a, slot, 1);
+    block_barrier<NR>(a, rank, ++epoch, err);
+    trace_mark(a, slot, 2);
+
     for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < a.nvec; t0 += (int64_t)gridDim.x * tile) {
         vec16 v[U][R];
 #pragma unroll
@@ -244,8 +369,22 @@ __global__ void __launch_bounds__(512, 1) oneshot_kernel(const __grid_constant__
             }
         }
     }
+    trace_mark(a, slot, 3);
     if (a.end_barrier) block_barrier<NR>(a, rank, ++epoch, err);
+    trace_mark(a, slot, 4);
     if (threadIdx.x == 0) state[blockIdx.x] = epoch;
+    trace_mark(a, slot, 5);
+}
+
+template <typename T, int NR, bool EMU>
+__global__ void __launch_bounds__(512, 1) oneshot_kernel(const __grid_constant__ CommArgs a) {
+    oneshot_body<T, NR, EMU, false>(a, nullptr, nullptr);
+}
+template <typename T, int NR, bool EMU>
+__global__ void __launch_bounds__(512, 1) oneshot_pack_kernel(const __grid_constant__ CommArgs a,
+                                                              const __grid_constant__ TensorTable tab) {
+    __shared__ TableSmem ts;
+    oneshot_body<T, NR, EMU, true>(a, &tab, &ts);
 }
 
 // ---- nvls (multimem) ------------------------------------------------------------------------------
@@ -267,14 +406,15 @@ __device__ __forceinline__ void multimem_st<float>(void* mc, const float* acc) {
                  "f"(acc[2]), "f"(acc[3])
                  : "memory");
 }
-template <>
-__device__ __forceinline__ void multimem_ld_reduce<__nv_bfloat16>(const void* mc, float* acc) {
-    vec16 v;  // the switch accumulates in fp32 and returns bf16x2
+// 16-bit: the switch accumulates in fp32 and returns bf16x2; the raw words are kept until all the
+// loads of a tile have been issued so that the conversion does not serialise them
+__device__ __forceinline__ vec16 multimem_ld_reduce_bf16_raw(const void* mc) {
+    vec16 v;
     asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
                  : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                  : "l"(mc)
                  : "memory");
-    VecOf<__nv_bfloat16>::to_float(v, acc);
+    return v;
 }
 template <>
 __device__ __forceinline__ void multimem_st<__nv_bfloat16>(void* mc, const float* acc) {
@@ -284,48 +424,106 @@ __device__ __forceinline__ void multimem_st<__nv_bfloat16>(void* mc, const float
                  : "memory");
 }
 
-template <typename T, int NR>
-__global__ void __launch_bounds__(512, 1) nvls_kernel(const __grid_constant__ CommArgs a) {
+// UT switch reductions in flight per thread; the tile (blockDim x UT vectors) is also the unit of
+// the pack prologue and of the SGD epilogue, so the same-numbered-CTA argument holds for any UT.
+template <typename T, int UT, bool PACK>
+__device__ __forceinline__ void nvls_body(const CommArgs& a, const TensorTable* tab, TableSmem* ts) {
     constexpr int N = VecOf<T>::N;
-    constexpr int U = 4;
-    const int nr = ranks_of<NR>(a);
+    const int nr = a.nranks;
     const int rank = a.rank;
     uint32_t* state = a.state;
     uint32_t* err = state + DLB_MAX_BLOCKS;
     uint32_t epoch = state[blockIdx.x];
 
-    block_barrier<NR>(a, rank, ++epoch, err);
+    trace_mark(a, 0, 0);
+    if (PACK) {
+        table_stage(*ts, *tab, 0);
+        pack_columns<T, UT>(a, *ts, tab->ntensors, reinterpret_cast<char*>(a.buf[rank]), nr);
+    }
+    trace_mark(a, 0, 1);
+    block_barrier<0>(a, rank, ++epoch, err);
+    trace_mark(a, 0, 2);
 
     const int64_t slice = (a.nvec + nr - 1) / nr;
     const int64_t begin = rank * slice, end = min(begin + slice, a.nvec);
-    // same column partition as two-shot (tile = blockDim * Unroll<NR>::U) so the epilogue matches
-    const int64_t tile = (int64_t)blockDim.x * Unroll<NR>::U;
+    const int64_t tile = (int64_t)blockDim.x * UT;
     char* mc = reinterpret_cast<char*>(a.mc);
     for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < slice; t0 += (int64_t)gridDim.x * tile) {
-        for (int64_t i0 = 0; i0 < tile; i0 += (int64_t)blockDim.x * U) {
-            float acc[U][N];
+        vec16 raw[UT];
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int64_t off = i0 + (int64_t)u * blockDim.x + threadIdx.x;
-                const int64_t j = begin + t0 + off;
-                if (off < tile && j < end) multimem_ld_reduce<T>(mc + j * 16, acc[u]);
-            }
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int64_t off = i0 + (int64_t)u * blockDim.x + threadIdx.x;
-                const int64_t j = begin + t0 + off;
-                if (off < tile && j < end) {
-#pragma unroll
-                    for (int i = 0; i < N; ++i) acc[u][i] *= a.scale;
-                    multimem_st<T>(mc + j * 16, acc[u]);
+        for (int u = 0; u < UT; ++u) {
+            const int64_t j = begin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
+            if (j < end) {
+                if (sizeof(T) == 4) {
+                    float f[4];
+                    multimem_ld_reduce<float>(mc + j * 16, f);
+                    raw[u] = VecOf<float>::from_float(f);
+                } else {
+                    raw[u] = multimem_ld_reduce_bf16_raw(mc + j * 16);
                 }
             }
         }
+#pragma unroll
+        for (int u = 0; u < UT; ++u) {
+            const int64_t j = begin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
+            if (j < end) {
+                float acc[N];
+                VecOf<T>::to_float(raw[u], acc);
+#pragma unroll
+                for (int i = 0; i < N; ++i) acc[i] *= a.scale;
+                multimem_st<T>(mc + j * 16, acc);
+            }
+        }
     }
+    trace_mark(a, 0, 3);
 
-    block_barrier<NR>(a, rank, ++epoch, err);
+    block_barrier<0>(a, rank, ++epoch, err);
+    trace_mark(a, 0, 4);
 
-    if (a.has_sgd) sgd_epilogue<T, NR>(a, a.sgd[0], reinterpret_cast<const char*>(a.buf[rank]), slice, tile);
+    if (a.has_sgd) sgd_epilogue<T, UT>(a, a.sgd[0], reinterpret_cast<const char*>(a.buf[rank]), nr);
+    if (threadIdx.x == 0) state[blockIdx.x] = epoch;
+    trace_mark(a, 0, 5);
+}
+
+template <typename T, int UT>
+__global__ void __launch_bounds__(512, 1) nvls_kernel(const __grid_constant__ CommArgs a) {
+    nvls_body<T, UT, false>(a, nullptr, nullptr);
+}
+template <typename T, int UT>
+__global__ void __launch_bounds__(512, 1) nvls_pack_kernel(const __grid_constant__ CommArgs a,
+                                                           const __grid_constant__ TensorTable tab) {
+    __shared__ TableSmem ts;
+    nvls_body<T, UT, true>(a, &tab, &ts);
+}
+
+// ---- broadcast: every rank copies `root`'s buffer into its own ---------------------------------------
+// Used at bring-up to give every replica rank 0's parameters without any other communication
+// library (reference: replicas rely on the same seed, src/main.py:31-34).
+__global__ void __launch_bounds__(512, 1) broadcast_kernel(const __grid_constant__ CommArgs a) {
+    uint32_t* state = a.state;
+    uint32_t* err = state + DLB_MAX_BLOCKS;
+    uint32_t epoch = state[blockIdx.x];
+    block_barrier<0>(a, a.rank, ++epoch, err);  // the root's buffer is filled
+    if (a.rank != a.root) {
+        const char* src = reinterpret_cast<const char*>(a.buf[a.root]);
+        char* dst = reinterpret_cast<char*>(a.buf[a.rank]);
+        constexpr int U = 8;
+        const int64_t tile = (int64_t)blockDim.x * U;
+        for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < a.nvec; t0 += (int64_t)gridDim.x * tile) {
+            vec16 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t j = t0 + (int64_t)u * blockDim.x + threadIdx.x;
+                if (j < a.nvec) v[u] = ld_vec_stream(src + j * 16);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t j = t0 + (int64_t)u * blockDim.x + threadIdx.x;
+                if (j < a.nvec) st_vec(dst + j * 16, v[u]);
+            }
+        }
+    }
+    block_barrier<0>(a, a.rank, ++epoch, err);  // everyone has its copy: the root may refill its buffer
     if (threadIdx.x == 0) state[blockIdx.x] = epoch;
 }
 
@@ -348,6 +546,7 @@ int fill_args(CommArgs& a, void* const* bufs, void* const* sigs, uint32_t* state
     const int per_vec = 16 / dlb_dtype_size(dtype);
     DLB_REQUIRE(numel >= 0 && numel % per_vec == 0, DLB_E_ARG, "%s: numel %lld is not a multiple of %d (16 bytes)", who, (long long)numel, per_vec);
     DLB_REQUIRE(state != nullptr, DLB_E_ARG, "%s: null state", who);
+    DLB_REQUIRE(sigs != nullptr, DLB_E_ARG, "%s: null signal pads", who);
     for (int r = 0; r < nranks; ++r) {
         DLB_REQUIRE(sigs[r] != nullptr, DLB_E_ARG, "%s: null signal pad for rank %d", who, r);
         DLB_REQUIRE(bufs == nullptr || (bufs[r] != nullptr && (reinterpret_cast<uintptr_t>(bufs[r]) & 15) == 0), DLB_E_ARG,
@@ -358,12 +557,15 @@ int fill_args(CommArgs& a, void* const* bufs, void* const* sigs, uint32_t* state
     }
     a.state = state;
     a.mc = nullptr;
+    a.trace = nullptr;
     a.nvec = numel / per_vec;
     a.timeout_ns = wait_timeout_ns();
     a.scale = scale;
+    a.pack_scale = 1.f;
     a.rank = rank;
     a.nranks = nranks;
     a.end_barrier = 0;
+    a.root = 0;
     a.has_sgd = sgd != nullptr;
     if (sgd) {
         DLB_REQUIRE(sgd->param && sgd->momentum_buf, DLB_E_ARG, "%s: fused SGD needs param and momentum", who);
@@ -372,43 +574,58 @@ int fill_args(CommArgs& a, void* const* bufs, void* const* sigs, uint32_t* state
     return 0;
 }
 
-using KernelFn = void (*)(const CommArgs);
-
-int launch(KernelFn k, dim3 grid, int threads, cudaStream_t stream, const CommArgs& a, bool cooperative) {
-    void* params[] = {const_cast<CommArgs*>(&a)};
+int launch(const void* k, dim3 grid, int threads, cudaStream_t stream, const CommArgs& a, const TensorTable* tab,
+           bool cooperative) {
+    void* params[] = {const_cast<CommArgs*>(&a), const_cast<TensorTable*>(tab)};
     if (cooperative)
-        DLB_CUDA(cudaLaunchCooperativeKernel((const void*)k, grid, dim3(threads), params, 0, stream));
+        DLB_CUDA(cudaLaunchCooperativeKernel(k, grid, dim3(threads), params, 0, stream));
     else
-        DLB_CUDA(cudaLaunchKernel((const void*)k, grid, dim3(threads), params, 0, stream));
+        DLB_CUDA(cudaLaunchKernel(k, grid, dim3(threads), params, 0, stream));
     return 0;
 }
 
-template <typename T, bool EMU>
-KernelFn pick_twoshot(int nranks) {
-    switch (nranks) {
-        case 2: return twoshot_kernel<T, 2, EMU>;
-        case 4: return twoshot_kernel<T, 4, EMU>;
-        case 8: return twoshot_kernel<T, 8, EMU>;
-        default: return twoshot_kernel<T, 0, EMU>;
-    }
+#define PICK_NR(KERNEL, T, EMU, nranks)                                     \
+    ((nranks) == 2   ? (const void*)KERNEL<T, 2, EMU>                       \
+     : (nranks) == 4 ? (const void*)KERNEL<T, 4, EMU>                       \
+     : (nranks) == 8 ? (const void*)KERNEL<T, 8, EMU>                       \
+                     : (const void*)KERNEL<T, 0, EMU>)
+
+template <bool EMU>
+const void* pick_twoshot(int dtype, int nranks, bool pack) {
+    if (dtype == DLB_F32) return pack ? PICK_NR(twoshot_pack_kernel, float, EMU, nranks) : PICK_NR(twoshot_kernel, float, EMU, nranks);
+    return pack ? PICK_NR(twoshot_pack_kernel, __nv_bfloat16, EMU, nranks) : PICK_NR(twoshot_kernel, __nv_bfloat16, EMU, nranks);
 }
-template <typename T, bool EMU>
-KernelFn pick_oneshot(int nranks) {
-    switch (nranks) {
-        case 2: return oneshot_kernel<T, 2, EMU>;
-        case 4: return oneshot_kernel<T, 4, EMU>;
-        case 8: return oneshot_kernel<T, 8, EMU>;
-        default: return oneshot_kernel<T, 0, EMU>;
-    }
+template <bool EMU>
+const void* pick_oneshot(int dtype, int nranks, bool pack) {
+    if (dtype == DLB_F32) return pack ? PICK_NR(oneshot_pack_kernel, float, EMU, nranks) : PICK_NR(oneshot_kernel, float, EMU, nranks);
+    return pack ? PICK_NR(oneshot_pack_kernel, __nv_bfloat16, EMU, nranks) : PICK_NR(oneshot_kernel, __nv_bfloat16, EMU, nranks);
 }
-template <typename T>
-KernelFn pick_nvls(int nranks) {
-    switch (nranks) {
-        case 2: return nvls_kernel<T, 2>;
-        case 4: return nvls_kernel<T, 4>;
-        case 8: return nvls_kernel<T, 8>;
-        default: return nvls_kernel<T, 0>;
-    }
+
+#define PICK_UT(KERNEL, T, ut) ((ut) == 2 ? (const void*)KERNEL<T, 2> : (ut) == 4 ? (const void*)KERNEL<T, 4> : (const void*)KERNEL<T, 8>)
+
+const void* pick_nvls(int dtype, int unroll, bool pack) {
+    if (dtype == DLB_F32) return pack ? PICK_UT(nvls_pack_kernel, float, unroll) : PICK_UT(nvls_kernel, float, unroll);
+    return pack ? PICK_UT(nvls_pack_kernel, __nv_bfloat16, unroll) : PICK_UT(nvls_kernel, __nv_bfloat16, unroll);
+}
+
+// Fill the kernel's tensor table for the fused pack prologue.  Returns 0 and has_pack = false when
+// there is nothing to pack.
+int fill_pack(TensorTable& tab, bool* has_pack, int dtype, int64_t numel, void* const* tensors, const int* tensor_dtypes,
+              const int64_t* offsets, const int64_t* numels, int ntensors, const char* who) {
+    *has_pack = false;
+    if (ntensors <= 0) return 0;
+    DLB_REQUIRE(ntensors <= DLB_MAX_TENSORS, DLB_E_LIMIT, "%s: %d tensors in the fused pack, at most %d (pack separately)", who,
+                ntensors, DLB_MAX_TENSORS);
+    DLB_REQUIRE(tensors && tensor_dtypes && offsets && numels, DLB_E_ARG, "%s: null tensor table", who);
+    bool aligned = false;
+    uint32_t first = 0, end = 0;
+    int rc = dlb_fill_table(tab, dtype, tensors, tensor_dtypes, offsets, numels, 0, ntensors, &aligned, &first, &end);
+    if (rc) return rc;
+    if (tab.ntensors == 0) return 0;
+    DLB_REQUIRE(aligned, DLB_E_ARG, "%s: the fused pack needs ascending, non-overlapping offsets on 16-byte boundaries of the buffer", who);
+    DLB_REQUIRE((int64_t)end <= numel, DLB_E_ARG, "%s: tensor table reaches element %u, beyond the buffer's %lld", who, end, (long long)numel);
+    *has_pack = true;
+    return 0;
 }
 
 }  // namespace
@@ -430,51 +647,118 @@ extern "C" int dlb_comm_check(uint32_t* state, void* stream) {
     return 0;
 }
 
+// ---- the general entry point ----------------------------------------------------------------------------
+extern "C" int dlb_allreduce(const dlb_allreduce_desc_t* d, void* stream) {
+    DLB_REQUIRE(d != nullptr, DLB_E_ARG, "dlb_allreduce: null descriptor");
+    const char* who = d->algo == DLB_ALGO_TWOSHOT ? "dlb_allreduce(twoshot)" : d->algo == DLB_ALGO_ONESHOT ? "dlb_allreduce(oneshot)" : "dlb_allreduce(nvls)";
+    DLB_REQUIRE(d->algo == DLB_ALGO_TWOSHOT || d->algo == DLB_ALGO_ONESHOT || d->algo == DLB_ALGO_NVLS, DLB_E_ARG,
+                "dlb_allreduce: unknown algo %d", d->algo);
+    DLB_REQUIRE(d->bufs != nullptr, DLB_E_ARG, "%s: null bufs", who);
+    CommArgs a;
+    int rc = fill_args(a, d->bufs, d->sigs, d->state, d->rank, d->nranks, d->numel, d->dtype, d->scale, d->nblocks, d->nthreads, d->sgd, who);
+    if (rc || a.nvec == 0) return rc;
+    const int unroll = d->unroll == 0 ? 4 : d->unroll;
+    DLB_REQUIRE(d->algo != DLB_ALGO_NVLS || unroll == 2 || unroll == 4 || unroll == 8, DLB_E_ARG, "%s: unroll %d (2, 4 or 8)", who, unroll);
+    TensorTable tab;
+    bool pack = false;
+    rc = fill_pack(tab, &pack, d->dtype, d->numel, d->tensors, d->tensor_dtypes, d->offsets, d->numels, d->ntensors, who);
+    if (rc) return rc;
+    a.pack_scale = d->pack_scale == 0.f ? 1.f : d->pack_scale;
+    a.trace = d->trace;
+    const void* k = nullptr;
+    if (d->algo == DLB_ALGO_TWOSHOT) {
+        k = pick_twoshot<false>(d->dtype, d->nranks, pack);
+    } else if (d->algo == DLB_ALGO_ONESHOT) {
+        DLB_REQUIRE(d->out != nullptr || d->sgd != nullptr, DLB_E_ARG, "%s: neither an output buffer nor a fused update", who);
+        DLB_REQUIRE(d->out != d->bufs[d->rank], DLB_E_ARG, "%s: out may not alias the input buffer (peers are reading it)", who);
+        DLB_REQUIRE((reinterpret_cast<uintptr_t>(d->out) & 15) == 0, DLB_E_ARG, "%s: out is not 16-byte aligned", who);
+        a.out[0] = d->out;
+        a.end_barrier = d->end_barrier;
+        k = pick_oneshot<false>(d->dtype, d->nranks, pack);
+    } else {
+        DLB_REQUIRE(d->mc_buf != nullptr && (reinterpret_cast<uintptr_t>(d->mc_buf) & 15) == 0, DLB_E_ARG,
+                    "%s: multicast pointer null or not 16-byte aligned", who);
+        a.mc = d->mc_buf;
+        k = pick_nvls(d->dtype, unroll, pack);
+    }
+    return launch(k, dim3(d->nblocks), d->nthreads, (cudaStream_t)stream, a, pack ? &tab : nullptr, false);
+}
+
+// ---- the original entry points: thin wrappers ------------------------------------------------------------
+static void base_desc(dlb_allreduce_desc_t& d, int algo, void* const* bufs, void* const* sigs, uint32_t* state, int rank,
+                      int nranks, int64_t numel, int dtype, float scale, int nblocks, int nthreads, const dlb_fused_sgd_t* sgd) {
+    d = dlb_allreduce_desc_t{};
+    d.algo = algo;
+    d.bufs = bufs;
+    d.sigs = sigs;
+    d.state = state;
+    d.rank = rank;
+    d.nranks = nranks;
+    d.numel = numel;
+    d.dtype = dtype;
+    d.scale = scale;
+    d.nblocks = nblocks;
+    d.nthreads = nthreads;
+    d.sgd = sgd;
+    d.pack_scale = 1.f;
+}
+
 extern "C" int dlb_allreduce_twoshot(void* const* bufs, void* const* sigs, uint32_t* state, int rank, int nranks,
                                      int64_t numel, int dtype, float scale, int nblocks, int nthreads,
                                      const dlb_fused_sgd_t* sgd, void* stream) {
-    CommArgs a;
-    DLB_REQUIRE(bufs != nullptr, DLB_E_ARG, "dlb_allreduce_twoshot: null bufs");
-    int rc = fill_args(a, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd, "dlb_allreduce_twoshot");
-    if (rc || a.nvec == 0) return rc;
-    KernelFn k = dtype == DLB_F32 ? pick_twoshot<float, false>(nranks) : pick_twoshot<__nv_bfloat16, false>(nranks);
-    return launch(k, dim3(nblocks), nthreads, (cudaStream_t)stream, a, false);
+    dlb_allreduce_desc_t d;
+    base_desc(d, DLB_ALGO_TWOSHOT, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd);
+    return dlb_allreduce(&d, stream);
 }
 
 extern "C" int dlb_allreduce_oneshot(void* const* bufs, void* out, void* const* sigs, uint32_t* state, int rank,
                                      int nranks, int64_t numel, int dtype, float scale, int nblocks, int nthreads,
                                      int end_barrier, const dlb_fused_sgd_t* sgd, void* stream) {
-    CommArgs a;
-    DLB_REQUIRE(bufs != nullptr, DLB_E_ARG, "dlb_allreduce_oneshot: null bufs");
-    int rc = fill_args(a, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd, "dlb_allreduce_oneshot");
-    if (rc || a.nvec == 0) return rc;
-    DLB_REQUIRE(out != nullptr || sgd != nullptr, DLB_E_ARG, "dlb_allreduce_oneshot: neither an output buffer nor a fused update");
-    DLB_REQUIRE(out != bufs[rank], DLB_E_ARG, "dlb_allreduce_oneshot: out may not alias the input buffer (peers are reading it)");
-    DLB_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, DLB_E_ARG, "dlb_allreduce_oneshot: out is not 16-byte aligned");
-    a.out[0] = out;
-    a.end_barrier = end_barrier;
-    KernelFn k = dtype == DLB_F32 ? pick_oneshot<float, false>(nranks) : pick_oneshot<__nv_bfloat16, false>(nranks);
-    return launch(k, dim3(nblocks), nthreads, (cudaStream_t)stream, a, false);
+    dlb_allreduce_desc_t d;
+    base_desc(d, DLB_ALGO_ONESHOT, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd);
+    d.out = out;
+    d.end_barrier = end_barrier;
+    return dlb_allreduce(&d, stream);
 }
 
 extern "C" int dlb_allreduce_nvls(void* mc_buf, void* const* bufs, void* const* sigs, uint32_t* state, int rank,
                                   int nranks, int64_t numel, int dtype, float scale, int nblocks, int nthreads,
                                   const dlb_fused_sgd_t* sgd, void* stream) {
-    CommArgs a;
-    DLB_REQUIRE(bufs != nullptr && mc_buf != nullptr, DLB_E_ARG, "dlb_allreduce_nvls: null buffer");
-    DLB_REQUIRE((reinterpret_cast<uintptr_t>(mc_buf) & 15) == 0, DLB_E_ARG, "dlb_allreduce_nvls: multicast pointer not 16-byte aligned");
-    int rc = fill_args(a, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd, "dlb_allreduce_nvls");
-    if (rc || a.nvec == 0) return rc;
-    a.mc = mc_buf;
-    KernelFn k = dtype == DLB_F32 ? pick_nvls<float>(nranks) : pick_nvls<__nv_bfloat16>(nranks);
-    return launch(k, dim3(nblocks), nthreads, (cudaStream_t)stream, a, false);
+    dlb_allreduce_desc_t d;
+    base_desc(d, DLB_ALGO_NVLS, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd);
+    d.mc_buf = mc_buf;
+    d.unroll = 4;
+    return dlb_allreduce(&d, stream);
+}
+
+// the "deep" variant of round 1 is the same kernel with eight reductions in flight per thread
+extern "C" int dlb_allreduce_nvls_deep(void* mc_buf, void* const* bufs, void* const* sigs, uint32_t* state, int rank,
+                                       int nranks, int64_t numel, int dtype, float scale, int nblocks, int nthreads,
+                                       const dlb_fused_sgd_t* sgd, void* stream) {
+    dlb_allreduce_desc_t d;
+    base_desc(d, DLB_ALGO_NVLS, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd);
+    d.mc_buf = mc_buf;
+    d.unroll = 8;
+    return dlb_allreduce(&d, stream);
 }
 
 extern "C" int dlb_barrier(void* const* sigs, uint32_t* state, int rank, int nranks, int nblocks, void* stream) {
     CommArgs a;
     int rc = fill_args(a, nullptr, sigs, state, rank, nranks, 0, DLB_F32, 1.f, nblocks, 32, nullptr, "dlb_barrier");
     if (rc) return rc;
-    return launch(barrier_kernel, dim3(nblocks), 32, (cudaStream_t)stream, a, false);
+    return launch((const void*)barrier_kernel, dim3(nblocks), 32, (cudaStream_t)stream, a, nullptr, false);
+}
+
+extern "C" int dlb_broadcast(void* const* bufs, void* const* sigs, uint32_t* state, int rank, int nranks, int root,
+                             int64_t nbytes, int nblocks, int nthreads, void* stream) {
+    CommArgs a;
+    DLB_REQUIRE(bufs != nullptr, DLB_E_ARG, "dlb_broadcast: null bufs");
+    DLB_REQUIRE(root >= 0 && root < nranks, DLB_E_ARG, "dlb_broadcast: root %d of %d", root, nranks);
+    DLB_REQUIRE(nbytes >= 0 && nbytes % 16 == 0, DLB_E_ARG, "dlb_broadcast: %lld bytes is not a multiple of 16", (long long)nbytes);
+    int rc = fill_args(a, bufs, sigs, state, rank, nranks, nbytes / 4, DLB_F32, 1.f, nblocks, nthreads, nullptr, "dlb_broadcast");
+    if (rc || a.nvec == 0) return rc;
+    a.root = root;
+    return launch((const void*)broadcast_kernel, dim3(nblocks), nthreads, (cudaStream_t)stream, a, nullptr, false);
 }
 
 // One-shot outputs in the emulation follow dlb_allreduce_oneshot's rules: 16-byte stores, and nobody
@@ -502,36 +786,59 @@ extern "C" size_t dlb_emulated_flags_bytes(int nranks) {
 }
 
 // Layout of the emulation scratch: nranks signal pads, then nranks state blocks.
-extern "C" int dlb_allreduce_emulated(int algo, void* const* bufs, void* const* outs, const dlb_fused_sgd_t* sgds,
-                                      void* flags, int nranks, int64_t numel, int dtype, float scale, int nblocks,
-                                      int nthreads, void* stream) {
-    DLB_REQUIRE(flags != nullptr && bufs != nullptr, DLB_E_ARG, "dlb_allreduce_emulated: null argument");
-    DLB_REQUIRE(algo == 0 || algo == 1, DLB_E_ARG, "dlb_allreduce_emulated: algo must be 0 (two-shot) or 1 (one-shot)");
+extern "C" int dlb_allreduce_emulated_ex(const dlb_emulated_desc_t* d, void* stream) {
+    DLB_REQUIRE(d != nullptr, DLB_E_ARG, "dlb_allreduce_emulated: null descriptor");
+    DLB_REQUIRE(d->flags != nullptr && d->bufs != nullptr, DLB_E_ARG, "dlb_allreduce_emulated: null argument");
+    DLB_REQUIRE(d->algo == DLB_ALGO_TWOSHOT || d->algo == DLB_ALGO_ONESHOT, DLB_E_ARG,
+                "dlb_allreduce_emulated: algo must be 0 (two-shot) or 1 (one-shot)");
+    const int nranks = d->nranks;
     DLB_REQUIRE(nranks >= 1 && nranks <= DLB_MAX_RANKS, DLB_E_LIMIT, "dlb_allreduce_emulated: nranks %d outside 1..%d", nranks, DLB_MAX_RANKS);
     void* sigs[DLB_MAX_RANKS];
-    char* base = reinterpret_cast<char*>(flags);
+    char* base = reinterpret_cast<char*>(d->flags);
     for (int r = 0; r < nranks; ++r) sigs[r] = base + (size_t)r * DLB_SIGNAL_BYTES;
     uint32_t* state = reinterpret_cast<uint32_t*>(base + (size_t)nranks * DLB_SIGNAL_BYTES);
     CommArgs a;
-    int rc = fill_args(a, bufs, sigs, state, 0, nranks, numel, dtype, scale, nblocks, nthreads, nullptr, "dlb_allreduce_emulated");
+    int rc = fill_args(a, d->bufs, sigs, state, 0, nranks, d->numel, d->dtype, d->scale, d->nblocks, d->nthreads, nullptr, "dlb_allreduce_emulated");
     if (rc || a.nvec == 0) return rc;
-    if (sgds) {
+    if (d->sgds) {
         a.has_sgd = 1;
-        for (int r = 0; r < nranks; ++r) a.sgd[r] = sgds[r];
+        for (int r = 0; r < nranks; ++r) a.sgd[r] = d->sgds[r];
     }
-    if (algo == 1) {
-        rc = check_emulated_outs(bufs, outs, sgds != nullptr, nranks);
+    if (d->algo == DLB_ALGO_ONESHOT) {
+        rc = check_emulated_outs(d->bufs, d->outs, d->sgds != nullptr, nranks);
         if (rc) return rc;
-        for (int r = 0; r < nranks; ++r) a.out[r] = outs ? outs[r] : nullptr;
+        for (int r = 0; r < nranks; ++r) a.out[r] = d->outs ? d->outs[r] : nullptr;
         a.end_barrier = 1;
     }
+    TensorTable tab;
+    bool pack = false;
+    rc = fill_pack(tab, &pack, d->dtype, d->numel, d->tensors, d->tensor_dtypes, d->offsets, d->numels, d->ntensors, "dlb_allreduce_emulated");
+    if (rc) return rc;
+    tab.emu_stacked = 1;
+    a.pack_scale = d->pack_scale == 0.f ? 1.f : d->pack_scale;
+    a.trace = d->trace;
     // all nranks * nblocks CTAs must be co-resident: that is what the cooperative launch checks
-    KernelFn k;
-    if (algo == 0)
-        k = dtype == DLB_F32 ? pick_twoshot<float, true>(nranks) : pick_twoshot<__nv_bfloat16, true>(nranks);
-    else
-        k = dtype == DLB_F32 ? pick_oneshot<float, true>(nranks) : pick_oneshot<__nv_bfloat16, true>(nranks);
-    return launch(k, dim3(nblocks, nranks), nthreads, (cudaStream_t)stream, a, true);
+    const void* k = d->algo == DLB_ALGO_TWOSHOT ? pick_twoshot<true>(d->dtype, nranks, pack) : pick_oneshot<true>(d->dtype, nranks, pack);
+    return launch(k, dim3(d->nblocks, nranks), d->nthreads, (cudaStream_t)stream, a, pack ? &tab : nullptr, true);
+}
+
+extern "C" int dlb_allreduce_emulated(int algo, void* const* bufs, void* const* outs, const dlb_fused_sgd_t* sgds,
+                                      void* flags, int nranks, int64_t numel, int dtype, float scale, int nblocks,
+                                      int nthreads, void* stream) {
+    dlb_emulated_desc_t d = {};
+    d.algo = algo;
+    d.bufs = bufs;
+    d.outs = outs;
+    d.sgds = sgds;
+    d.flags = flags;
+    d.nranks = nranks;
+    d.numel = numel;
+    d.dtype = dtype;
+    d.scale = scale;
+    d.nblocks = nblocks;
+    d.nthreads = nthreads;
+    d.pack_scale = 1.f;
+    return dlb_allreduce_emulated_ex(&d, stream);
 }
 
 // ---- dlb_allreduce_emulated_static: the emulated allreduce for callers that cannot allocate ---------
@@ -620,97 +927,4 @@ extern "C" int dlb_allreduce_emulated_static(int algo, void* const* bufs, void* 
     // the array keeps the last call's flags and epochs (possibly laid out for another rank count)
     DLB_CUDA(cudaMemsetAsync(flags, 0, used, (cudaStream_t)stream));
     return dlb_allreduce_emulated(algo, bufs, outs, nullptr, flags, nranks, numel, dtype, scale, nblocks, nthreads, stream);
-}
-
-// ---- EXPERIMENTAL: nvls with a deeper load pipeline ---------------------------------------------------
-//
-// Not selected by default and not yet measured on hardware (written after this round's GPU budget
-// was spent; `--algo nvls_deep` or DLB200_EXPERIMENTAL=1 opts in).  Motivation, from the 8-GPU sweep:
-// nvls_kernel shares its tile (blockDim x 2 vectors for 8 ranks) with the two-shot kernel so both can
-// use one epilogue partition, which leaves two multimem.ld_reduce in flight per thread, and the
-// tuner prefers 8-16 CTAs at 4-16 MiB: the variant is latency-bound there (29 % / 59 % of the NVLink
-// roofline).  Here the tile is blockDim x 8 vectors with all eight switch reductions issued before
-// the first multimem.st, and the epilogue walks the same larger tiles, so the same-numbered-CTA
-// argument for the barrier still holds.
-namespace {
-
-template <typename T, int NR>
-__global__ void __launch_bounds__(512, 1) nvls_deep_kernel(const __grid_constant__ CommArgs a) {
-    constexpr int N = VecOf<T>::N;
-    constexpr int U = 8;
-    const int nr = ranks_of<NR>(a);
-    const int rank = a.rank;
-    uint32_t* state = a.state;
-    uint32_t* err = state + DLB_MAX_BLOCKS;
-    uint32_t epoch = state[blockIdx.x];
-
-    block_barrier<NR>(a, rank, ++epoch, err);
-
-    const int64_t slice = (a.nvec + nr - 1) / nr;
-    const int64_t begin = rank * slice, end = min(begin + slice, a.nvec);
-    const int64_t tile = (int64_t)blockDim.x * U;
-    char* mc = reinterpret_cast<char*>(a.mc);
-    for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < slice; t0 += (int64_t)gridDim.x * tile) {
-        float acc[U][N];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int64_t j = begin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
-            if (j < end) multimem_ld_reduce<T>(mc + j * 16, acc[u]);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int64_t j = begin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
-            if (j < end) {
-#pragma unroll
-                for (int i = 0; i < N; ++i) acc[u][i] *= a.scale;
-                multimem_st<T>(mc + j * 16, acc[u]);
-            }
-        }
-    }
-
-    block_barrier<NR>(a, rank, ++epoch, err);
-
-    if (a.has_sgd) {
-        const char* local = reinterpret_cast<const char*>(a.buf[rank]);
-        for (int sl = 0; sl < nr; ++sl) {
-            const int64_t sbegin = sl * slice, send = min(sbegin + slice, a.nvec);
-            for (int64_t t0 = (int64_t)blockIdx.x * tile; t0 < slice; t0 += (int64_t)gridDim.x * tile) {
-#pragma unroll 2
-                for (int u = 0; u < U; ++u) {
-                    const int64_t j = sbegin + t0 + (int64_t)u * blockDim.x + threadIdx.x;
-                    if (j < send) {
-                        float g[N];
-                        VecOf<T>::to_float(ld_vec(local + j * 16), g);
-                        sgd_apply_vec<N>(a.sgd[0], (size_t)j * N, g);
-                    }
-                }
-            }
-        }
-    }
-    if (threadIdx.x == 0) state[blockIdx.x] = epoch;
-}
-
-template <typename T>
-KernelFn pick_nvls_deep(int nranks) {
-    switch (nranks) {
-        case 2: return nvls_deep_kernel<T, 2>;
-        case 4: return nvls_deep_kernel<T, 4>;
-        case 8: return nvls_deep_kernel<T, 8>;
-        default: return nvls_deep_kernel<T, 0>;
-    }
-}
-
-}  // namespace
-
-extern "C" int dlb_allreduce_nvls_deep(void* mc_buf, void* const* bufs, void* const* sigs, uint32_t* state, int rank,
-                                       int nranks, int64_t numel, int dtype, float scale, int nblocks, int nthreads,
-                                       const dlb_fused_sgd_t* sgd, void* stream) {
-    CommArgs a;
-    DLB_REQUIRE(bufs != nullptr && mc_buf != nullptr, DLB_E_ARG, "dlb_allreduce_nvls_deep: null buffer");
-    DLB_REQUIRE((reinterpret_cast<uintptr_t>(mc_buf) & 15) == 0, DLB_E_ARG, "dlb_allreduce_nvls_deep: multicast pointer not 16-byte aligned");
-    int rc = fill_args(a, bufs, sigs, state, rank, nranks, numel, dtype, scale, nblocks, nthreads, sgd, "dlb_allreduce_nvls_deep");
-    if (rc || a.nvec == 0) return rc;
-    a.mc = mc_buf;
-    KernelFn k = dtype == DLB_F32 ? pick_nvls_deep<float>(nranks) : pick_nvls_deep<__nv_bfloat16>(nranks);
-    return launch(k, dim3(nblocks), nthreads, (cudaStream_t)stream, a, false);
 }

@@ -133,7 +133,8 @@ def _native_factory(overlap: bool, algo: str, config):
 
     return functools.partial(
         B200Dist, overlap=overlap, algo=algo if config.algo == "auto" else config.algo,
-        fused_sgd=bool(config.fused_sgd), comm_dtype=config.comm_dtype, model_dtype=config.dtype,
+        fused_sgd=bool(config.fused_sgd), fuse_pack=bool(getattr(config, "fuse_pack", 1)), comm_dtype=config.comm_dtype,
+        model_dtype=config.dtype,
         cuda_graph=bool(getattr(config, "cuda_graph", 0)), dynamic_unused=bool(getattr(config, "dynamic_unused", 0)))
 
 

@@ -37,6 +37,29 @@ class FusedSgd(ctypes.Structure):
     _fields_ = [("param", c_void_p), ("momentum_buf", c_void_p), ("shadow_bf16", c_void_p), ("hyper", SgdHyper)]
 
 
+class AllreduceDesc(ctypes.Structure):
+    """``dlb_allreduce_desc_t`` (include/dlb200.h)."""
+    _fields_ = [("algo", c_int), ("rank", c_int), ("nranks", c_int),
+                ("bufs", POINTER(c_void_p)), ("out", c_void_p), ("mc_buf", c_void_p), ("sigs", POINTER(c_void_p)),
+                ("state", c_void_p), ("numel", c_int64), ("dtype", c_int), ("scale", c_float),
+                ("nblocks", c_int), ("nthreads", c_int), ("unroll", c_int), ("end_barrier", c_int),
+                ("sgd", POINTER(FusedSgd)),
+                ("tensors", POINTER(c_void_p)), ("tensor_dtypes", POINTER(c_int)), ("offsets", POINTER(c_int64)),
+                ("numels", POINTER(c_int64)), ("ntensors", c_int), ("pack_scale", c_float), ("trace", c_void_p)]
+
+
+class EmulatedDesc(ctypes.Structure):
+    """``dlb_emulated_desc_t`` (include/dlb200.h)."""
+    _fields_ = [("algo", c_int), ("nranks", c_int),
+                ("bufs", POINTER(c_void_p)), ("outs", POINTER(c_void_p)), ("sgds", POINTER(FusedSgd)), ("flags", c_void_p),
+                ("numel", c_int64), ("dtype", c_int), ("scale", c_float), ("nblocks", c_int), ("nthreads", c_int),
+                ("tensors", POINTER(c_void_p)), ("tensor_dtypes", POINTER(c_int)), ("offsets", POINTER(c_int64)),
+                ("numels", POINTER(c_int64)), ("ntensors", c_int), ("pack_scale", c_float), ("trace", c_void_p)]
+
+
+ALGO_CODE = {"twoshot": 0, "oneshot": 1, "nvls": 2}
+
+
 class DlbError(RuntimeError):
     def __init__(self, code: int, message: str):
         super().__init__(f"libdlb200 error {code}: {message}")
@@ -77,6 +100,10 @@ _PROTOS = {
                          c_int, c_float, c_void_p]),
     "dlb_unpack": (c_int, [c_void_p, c_int, POINTER(c_void_p), POINTER(c_int), POINTER(c_int64), POINTER(c_int64),
                            c_int, c_float, c_void_p]),
+    "dlb_pack_ex": (c_int, [c_void_p, c_int, POINTER(c_void_p), POINTER(c_int), POINTER(c_int64), POINTER(c_int64),
+                            c_int, c_float, c_int, c_void_p]),
+    "dlb_unpack_ex": (c_int, [c_void_p, c_int, POINTER(c_void_p), POINTER(c_int), POINTER(c_int64), POINTER(c_int64),
+                              c_int, c_float, c_int, c_void_p]),
     "dlb_sgd_flat": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int64, POINTER(SgdHyper), c_void_p]),
     "dlb_sgd_multi": (c_int, [POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int),
                               POINTER(c_int64), c_int, POINTER(SgdHyper), c_void_p]),
@@ -88,6 +115,9 @@ _PROTOS = {
                                    c_int, c_float, c_int, c_int, POINTER(FusedSgd), c_void_p]),
     "dlb_allreduce_nvls_deep": (c_int, [c_void_p, POINTER(c_void_p), POINTER(c_void_p), c_void_p, c_int, c_int, c_int64,
                                         c_int, c_float, c_int, c_int, POINTER(FusedSgd), c_void_p]),
+    "dlb_allreduce": (c_int, [POINTER(AllreduceDesc), c_void_p]),
+    "dlb_allreduce_emulated_ex": (c_int, [POINTER(EmulatedDesc), c_void_p]),
+    "dlb_broadcast": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_int64, c_int, c_int, c_void_p]),
     "dlb_barrier": (c_int, [POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_void_p]),
     "dlb_set_wait_timeout_ms": (c_int, [c_int]),
     "dlb_comm_check": (c_int, [c_void_p, c_void_p]),

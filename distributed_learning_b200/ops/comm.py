@@ -24,8 +24,8 @@ from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
 
-from ._lib import (DLB_MAX_BLOCKS, DLB_MAX_RANKS, DLB_SIGNAL_BYTES, DLB_STATE_WORDS, DlbError, FusedSgd, check,
-                   dtype_code, lib, ptr_array, stream_handle)
+from ._lib import (ALGO_CODE, DLB_MAX_BLOCKS, DLB_MAX_RANKS, DLB_SIGNAL_BYTES, DLB_STATE_WORDS, AllreduceDesc, DlbError,
+                   EmulatedDesc, FusedSgd, check, dtype_code, lib, ptr_array, stream_handle)
 
 ALGOS = ("oneshot", "twoshot", "nvls")
 _ALIGN = 4096
@@ -60,6 +60,14 @@ def default_nblocks(nbytes: int, algo: str) -> int:
     return 48
 
 
+def default_unroll(nbytes: int) -> int:
+    """nvls pipeline depth when nothing was measured: deeper for larger messages."""
+    env = os.environ.get("DLB200_UNROLL")
+    if env:
+        return int(env)
+    return 4 if nbytes <= 2 << 20 else 8
+
+
 class _ModeFailed(RuntimeError):
     """An arena mode (vmm / ipc) failed on at least one rank; raised on every rank at the same vote."""
 
@@ -88,7 +96,7 @@ class NativeComm:
         self._sig_array = None
         self._buf_arrays: Dict[int, "ctypes.Array"] = {}
         self._handles: dict = {}
-        self.tuned: Dict[Tuple[int, int], Tuple[str, int]] = {}     # (dtype code, pow2 bytes) -> (algo, nblocks)
+        self.tuned: Dict[Tuple[int, int], Tuple[str, int, int]] = {}     # (dtype code, pow2 bytes) -> (algo, nblocks, unroll)
         self.launches = 0
         self.topology: Optional[dict] = None
 
@@ -352,56 +360,71 @@ class NativeComm:
     # ---------------------------------------------------------------------------------------
     # collectives
     # ---------------------------------------------------------------------------------------
-    def choose(self, nbytes: int, dtype: torch.dtype, algo: str = "auto") -> Tuple[str, int]:
-        """Variant and grid for a message: the measured table if ``tune`` filled it, else a
+    def choose(self, nbytes: int, dtype: torch.dtype, algo: str = "auto") -> Tuple[str, int, int]:
+        """``(variant, CTAs, unroll)`` for a message: the measured table if ``tune`` filled it, else a
         size heuristic (one-shot while latency dominates, NVLS when the switch can reduce)."""
         if algo != "auto":
-            if algo in ("nvls", "nvls_deep") and not self.has_multicast:
-                algo = "twoshot"
-            return algo, default_nblocks(nbytes, algo)
+            unroll = 8 if algo == "nvls_deep" else default_unroll(nbytes)
+            if algo in ("nvls", "nvls_deep"):
+                algo = "nvls" if self.has_multicast else "twoshot"
+            return algo, default_nblocks(nbytes, algo), unroll
         key = (dtype_code(dtype), max(nbytes, 1).bit_length())
         if key in self.tuned:
             return self.tuned[key]
         if nbytes <= (256 << 10) * 8 // max(self.world, 2):
-            return "oneshot", default_nblocks(nbytes, "oneshot")
+            return "oneshot", default_nblocks(nbytes, "oneshot"), 0
         if self.has_multicast:
-            return "nvls", default_nblocks(nbytes, "nvls")
-        return "twoshot", default_nblocks(nbytes, "twoshot")
+            return "nvls", default_nblocks(nbytes, "nvls"), default_unroll(nbytes)
+        return "twoshot", default_nblocks(nbytes, "twoshot"), 0
 
     def allreduce(self, offset: int, numel: int, dtype: torch.dtype, algo: str = "twoshot", scale: float = 1.0,
                   out_offset: Optional[int] = None, sgd: Optional[FusedSgd] = None, nblocks: Optional[int] = None,
-                  stream=None, end_barrier: bool = False) -> None:
+                  stream=None, end_barrier: bool = False, pack=None, pack_scale: float = 1.0, unroll: int = 0,
+                  trace: Optional[torch.Tensor] = None) -> None:
         """Sum ``numel`` elements at ``offset`` over all ranks (times ``scale``) on ``stream``.
 
         two-shot / nvls work in place; one-shot writes to ``out_offset``.  By default one-shot has
         no trailing barrier and the caller must alternate input buffers between consecutive uses;
         ``end_barrier=True`` adds the barrier so the same input buffer can be refilled right away
         (needed when a step is replayed from a CUDA graph).  ``sgd`` fuses the parameter update.
-        Every rank must make the same sequence of calls."""
-        L = lib()
+        ``pack`` (a ``PackPlan`` whose pointers have been set, see ``PackPlan.bind``) fuses the
+        gather of the bucket's gradient tensors into the kernel's prologue (times ``pack_scale``).
+        ``unroll`` (2/4/8) is the nvls variant's pipeline depth; ``trace`` an int64 tensor of 8
+        elements that receives the phase timestamps.  Every rank must make the same sequence of
+        calls with the same ``nblocks`` and ``unroll``."""
         esize = torch.empty((), dtype=dtype).element_size()
-        nblocks = nblocks or default_nblocks(numel * esize, algo)
-        sgd_p = ctypes.byref(sgd) if sgd is not None else None
-        st = stream_handle(stream)
-        code = dtype_code(dtype)
-        if algo == "twoshot":
-            check(L.dlb_allreduce_twoshot(self._bufs(offset), self._sig_array, self.state.data_ptr(), self.rank,
-                                          self.world, numel, code, scale, nblocks, self.nthreads, sgd_p, st))
-        elif algo == "oneshot":
+        if algo == "nvls_deep":
+            algo, unroll = "nvls", 8
+        if algo not in ALGO_CODE:
+            raise ValueError(f"unknown algo {algo!r}")
+        d = AllreduceDesc()
+        d.algo, d.rank, d.nranks = ALGO_CODE[algo], self.rank, self.world
+        d.bufs, d.sigs, d.state = self._bufs(offset), self._sig_array, self.state.data_ptr()
+        d.numel, d.dtype, d.scale = numel, dtype_code(dtype), scale
+        d.nblocks = nblocks or default_nblocks(numel * esize, algo)
+        d.nthreads, d.unroll, d.end_barrier = self.nthreads, unroll, int(end_barrier)
+        if sgd is not None:
+            d.sgd = ctypes.pointer(sgd)
+        if algo == "oneshot":
             if out_offset is None and sgd is None:
                 raise ValueError("one-shot needs out_offset (it cannot work in place)")
-            out = self.peer_ptrs[self.rank] + self.data_offset + out_offset if out_offset is not None else None
-            check(L.dlb_allreduce_oneshot(self._bufs(offset), out, self._sig_array, self.state.data_ptr(), self.rank,
-                                          self.world, numel, code, scale, nblocks, self.nthreads, int(end_barrier), sgd_p, st))
-        elif algo in ("nvls", "nvls_deep"):
+            d.out = self.peer_ptrs[self.rank] + self.data_offset + out_offset if out_offset is not None else None
+        elif algo == "nvls":
             if not self.has_multicast:
                 raise RuntimeError("nvls requested but no multicast mapping exists")
-            fn = L.dlb_allreduce_nvls if algo == "nvls" else L.dlb_allreduce_nvls_deep     # the latter is experimental
-            check(fn(self.mc_ptr + self.data_offset + offset, self._bufs(offset), self._sig_array,
-                                       self.state.data_ptr(), self.rank, self.world, numel, code, scale, nblocks,
-                                       self.nthreads, sgd_p, st))
-        else:
-            raise ValueError(f"unknown algo {algo!r}")
+            d.mc_buf = self.mc_ptr + self.data_offset + offset
+        if pack is not None:
+            d.tensors, d.tensor_dtypes, d.offsets, d.numels, d.ntensors = pack.ptrs, pack.dtypes, pack.offsets, pack.numels, pack.n
+            d.pack_scale = pack_scale
+        if trace is not None:
+            d.trace = trace.data_ptr()
+        check(lib().dlb_allreduce(ctypes.byref(d), stream_handle(stream)))
+        self.launches += 1
+
+    def broadcast(self, offset: int, nbytes: int, root: int = 0, stream=None, nblocks: int = 16) -> None:
+        """Every rank's arena bytes ``[offset, offset+nbytes)`` become a copy of ``root``'s (one kernel)."""
+        check(lib().dlb_broadcast(self._bufs(offset), self._sig_array, self.state.data_ptr(), self.rank, self.world, root,
+                                  nbytes, nblocks, self.nthreads, stream_handle(stream)))
         self.launches += 1
 
     def barrier(self, stream=None, nblocks: int = 1) -> None:
@@ -416,16 +439,22 @@ class NativeComm:
     # measured selection
     # ---------------------------------------------------------------------------------------
     def tune(self, sizes_bytes: Sequence[int], dtype: torch.dtype = torch.float32, iters: int = 10,
-             scratch_offset: int = 0, block_choices: Sequence[int] = (8, 16, 32, 48)) -> Dict[int, dict]:
-        """Collective.  Time every available variant (and grid) on each size, take the max over
-        ranks, and remember the fastest per size class.  Uses arena bytes
-        ``[scratch_offset, scratch_offset + 2*max(sizes))``; contents are destroyed."""
+             scratch_offset: int = 0, block_choices: Sequence[int] = (8, 16, 32, 48, 64),
+             unroll_choices: Sequence[int] = (4, 8), cache: bool = True) -> Dict[int, dict]:
+        """Collective.  Time every available variant (grid, and pipeline depth for nvls) on each size,
+        take the max over ranks, and remember the fastest per size class.  Uses arena bytes
+        ``[scratch_offset, scratch_offset + 2*max(sizes))``; contents are destroyed.  With ``cache``
+        the table is also read from / written to a JSON file (``$DLB200_TUNE_CACHE`` or a file in the
+        temp directory named after the GPU model and the world size), so later jobs on the same box
+        skip the measurement."""
         esize = torch.empty((), dtype=dtype).element_size()
         stream = torch.cuda.current_stream(self.device)
         report: Dict[int, dict] = {}
+        wanted = {(dtype_code(dtype), max(_round_up(n, 16), 1).bit_length()) for n in sizes_bytes}
+        if cache and self._load_tuned() and wanted <= set(self.tuned):
+            return {n: {"best": self.tuned[(dtype_code(dtype), max(_round_up(n, 16), 1).bit_length())], "cached": True}
+                    for n in sizes_bytes}
         algos = [a for a in ALGOS if a != "nvls" or self.has_multicast]
-        if self.has_multicast and os.environ.get("DLB200_EXPERIMENTAL"):
-            algos.append("nvls_deep")            # opt-in: not yet measured on hardware
         for nbytes in sizes_bytes:
             nbytes = _round_up(nbytes, 16)
             numel = nbytes // esize
@@ -435,17 +464,19 @@ class NativeComm:
                 if algo == "oneshot" and nbytes * self.world > 256 << 20:
                     continue
                 for nb in block_choices:
-                    def run():
-                        self.allreduce(scratch_offset, numel, dtype, algo, 1.0, out_offset=out_off, nblocks=nb, stream=stream)
-                    for _ in range(2):
-                        run()
-                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    e0.record(stream)
-                    for _ in range(iters):
-                        run()
-                    e1.record(stream)
-                    e1.synchronize()
-                    results[(algo, nb)] = e0.elapsed_time(e1) / iters
+                    for unroll in (unroll_choices if algo == "nvls" else (0,)):
+                        def run():
+                            self.allreduce(scratch_offset, numel, dtype, algo, 1.0, out_offset=out_off, nblocks=nb,
+                                           stream=stream, unroll=unroll)
+                        for _ in range(2):
+                            run()
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        e0.record(stream)
+                        for _ in range(iters):
+                            run()
+                        e1.record(stream)
+                        e1.synchronize()
+                        results[(algo, nb, unroll)] = e0.elapsed_time(e1) / iters
             keys = sorted(results)
             t = torch.tensor([results[k] for k in keys], dtype=torch.float64)
             if self.world > 1:
@@ -455,8 +486,62 @@ class NativeComm:
                 t = t.cpu()
             best = int(torch.argmin(t))
             self.tuned[(dtype_code(dtype), max(nbytes, 1).bit_length())] = keys[best]
-            report[nbytes] = {"best": keys[best], "ms": {f"{a}/{b}": float(v) for (a, b), v in zip(keys, t.tolist())}}
+            report[nbytes] = {"best": keys[best], "ms": {f"{a}/{b}/u{u}": float(v) for (a, b, u), v in zip(keys, t.tolist())}}
+        if cache:
+            self._save_tuned()
         return report
+
+    # the measured table on disk: {"<dtype code>:<size class>": [algo, nblocks, unroll]}
+    def _tune_cache_path(self) -> str:
+        import re
+        import tempfile
+
+        explicit = os.environ.get("DLB200_TUNE_CACHE")
+        if explicit:
+            return explicit
+        gpu = re.sub(r"[^A-Za-z0-9]+", "_", torch.cuda.get_device_name(self.device))
+        mc = "mc" if self.has_multicast else "nomc"
+        return os.path.join(tempfile.gettempdir(), f"dlb200_tune_{gpu}_n{self.world}_{mc}.json")
+
+    def _load_tuned(self) -> bool:
+        """Collective: rank 0 reads the file, every rank gets the same table (or none)."""
+        import json
+
+        table = None
+        if self.rank == 0:
+            try:
+                with open(self._tune_cache_path()) as f:
+                    table = json.load(f)
+            except (OSError, ValueError):
+                table = None
+        table = self._gather(table)[0] if self.world > 1 else table
+        if not table:
+            return False
+        for k, v in table.items():
+            code, cls = k.split(":")
+            if v[0] == "nvls" and not self.has_multicast:
+                continue
+            self.tuned.setdefault((int(code), int(cls)), (v[0], int(v[1]), int(v[2])))
+        return True
+
+    def _save_tuned(self) -> None:
+        import json
+
+        if self.rank != 0:
+            return
+        path = self._tune_cache_path()
+        try:
+            try:
+                with open(path) as f:
+                    table = json.load(f)
+            except (OSError, ValueError):
+                table = {}
+            table.update({f"{c}:{cls}": list(v) for (c, cls), v in self.tuned.items()})
+            with open(path + f".{os.getpid()}", "w") as f:
+                json.dump(table, f)
+            os.replace(path + f".{os.getpid()}", path)
+        except OSError:
+            pass                                   # a read-only temp directory only costs the next job a re-tune
 
     def close(self) -> None:
         if self.mode is None:
@@ -497,14 +582,29 @@ def emulated_flags(nranks: int, device) -> torch.Tensor:
 
 def emulated_allreduce(bufs: Sequence[torch.Tensor], algo: str = "twoshot", scale: float = 1.0,
                        outs: Optional[Sequence[torch.Tensor]] = None, sgds: Optional[Sequence[FusedSgd]] = None,
-                       flags: Optional[torch.Tensor] = None, nblocks: int = 4, nthreads: int = 256, stream=None) -> None:
-    """All ``len(bufs)`` ranks in one cooperative launch on one GPU (see ``dlb200.h``)."""
+                       flags: Optional[torch.Tensor] = None, nblocks: int = 4, nthreads: int = 256, stream=None,
+                       pack=None, pack_scale: float = 1.0, trace: Optional[torch.Tensor] = None) -> None:
+    """All ``len(bufs)`` ranks in one cooperative launch on one GPU (see ``dlb200.h``).  ``pack``: a
+    ``PackPlan`` bound to *stacked* tensors (tensor i stored as ``[nranks, numel_i]``, row r belonging
+    to emulated rank r) to run the fused pack prologue."""
     n = len(bufs)
     if flags is None:
         flags = emulated_flags(n, bufs[0].device)
-    B = ptr_array([b.data_ptr() for b in bufs])
-    O = ptr_array([o.data_ptr() for o in outs]) if outs is not None else None
-    S = (FusedSgd * n)(*sgds) if sgds is not None else None
-    check(lib().dlb_allreduce_emulated({"twoshot": 0, "oneshot": 1}[algo], B, O, S, flags.data_ptr(), n,
-                                       bufs[0].numel(), dtype_code(bufs[0].dtype), scale, nblocks, nthreads,
-                                       stream_handle(stream)))
+    d = EmulatedDesc()
+    d.algo, d.nranks = ALGO_CODE[algo], n
+    d.bufs = ptr_array([b.data_ptr() for b in bufs])
+    if outs is not None:
+        d.outs = ptr_array([o.data_ptr() for o in outs])
+    keep = None
+    if sgds is not None:
+        keep = (FusedSgd * n)(*sgds)
+        d.sgds = keep
+    d.flags = flags.data_ptr()
+    d.numel, d.dtype, d.scale = bufs[0].numel(), dtype_code(bufs[0].dtype), scale
+    d.nblocks, d.nthreads = nblocks, nthreads
+    if pack is not None:
+        d.tensors, d.tensor_dtypes, d.offsets, d.numels, d.ntensors = pack.ptrs, pack.dtypes, pack.offsets, pack.numels, pack.n
+        d.pack_scale = pack_scale
+    if trace is not None:
+        d.trace = trace.data_ptr()
+    check(lib().dlb_allreduce_emulated_ex(ctypes.byref(d), stream_handle(stream)))

@@ -16,6 +16,9 @@ import torch
 from ._lib import FusedSgd, SgdHyper, check, dtype_code, lib, stream_handle
 
 
+PACK_VARIANTS = {"auto": 0, "chunks": 1, "tiles": 2, "bulk": 3}
+
+
 class PackPlan:
     """Tables for packing/unpacking one list of tensors into/from one flat buffer."""
 
@@ -41,29 +44,39 @@ class PackPlan:
                     raise ValueError("pack/unpack need contiguous tensors")
                 ptrs[i] = t.data_ptr()
 
-    def pack(self, flat: torch.Tensor, tensors: Sequence[Optional[torch.Tensor]], scale: float = 1.0, stream=None) -> None:
-        """``flat[offset_i : offset_i+n_i] = cast(tensor_i * scale)``; a ``None`` tensor packs zeros."""
+    def bind(self, tensors: Sequence[Optional[torch.Tensor]]) -> "PackPlan":
+        """Point the table at this step's tensors (for the allreduce kernels' fused pack prologue)."""
         self._set_ptrs(tensors)
-        check(lib().dlb_pack(flat.data_ptr(), dtype_code(flat.dtype), self.ptrs, self.dtypes, self.offsets,
-                             self.numels, self.n, float(scale), stream_handle(stream)))
+        return self
 
-    def unpack(self, flat: torch.Tensor, tensors: Sequence[Optional[torch.Tensor]], scale: float = 1.0, stream=None) -> None:
+    def pack(self, flat: torch.Tensor, tensors: Sequence[Optional[torch.Tensor]], scale: float = 1.0, stream=None,
+             variant: str = "auto") -> None:
+        """``flat[offset_i : offset_i+n_i] = cast(tensor_i * scale)``; a ``None`` tensor packs zeros.
+        ``variant`` names the kernel (``PACK_VARIANTS``; see ``csrc/pack.cu``)."""
+        self._set_ptrs(tensors)
+        check(lib().dlb_pack_ex(flat.data_ptr(), dtype_code(flat.dtype), self.ptrs, self.dtypes, self.offsets,
+                                self.numels, self.n, float(scale), PACK_VARIANTS[variant], stream_handle(stream)))
+
+    def unpack(self, flat: torch.Tensor, tensors: Sequence[Optional[torch.Tensor]], scale: float = 1.0, stream=None,
+               variant: str = "auto") -> None:
         """``tensor_i = cast(flat[offset_i : offset_i+n_i] * scale)``; ``None`` tensors are skipped."""
         self._set_ptrs(tensors)
-        check(lib().dlb_unpack(flat.data_ptr(), dtype_code(flat.dtype), self.ptrs, self.dtypes, self.offsets,
-                               self.numels, self.n, float(scale), stream_handle(stream)))
+        check(lib().dlb_unpack_ex(flat.data_ptr(), dtype_code(flat.dtype), self.ptrs, self.dtypes, self.offsets,
+                                  self.numels, self.n, float(scale), PACK_VARIANTS[variant], stream_handle(stream)))
 
 
 def pack(flat: torch.Tensor, tensors: Sequence[Optional[torch.Tensor]], offsets: Sequence[int], scale: float = 1.0,
-         dtypes: Optional[Sequence[torch.dtype]] = None, numels: Optional[Sequence[int]] = None, stream=None) -> None:
+         dtypes: Optional[Sequence[torch.dtype]] = None, numels: Optional[Sequence[int]] = None, stream=None,
+         variant: str = "auto") -> None:
     """One-off pack (builds the tables on the fly)."""
     numels = numels or [t.numel() for t in tensors]
     dtypes = dtypes or [t.dtype for t in tensors]
-    PackPlan(numels, offsets, dtypes).pack(flat, tensors, scale, stream)
+    PackPlan(numels, offsets, dtypes).pack(flat, tensors, scale, stream, variant)
 
 
-def unpack(flat: torch.Tensor, tensors: Sequence[torch.Tensor], offsets: Sequence[int], scale: float = 1.0, stream=None) -> None:
-    PackPlan.for_tensors(tensors, offsets).unpack(flat, tensors, scale, stream)
+def unpack(flat: torch.Tensor, tensors: Sequence[torch.Tensor], offsets: Sequence[int], scale: float = 1.0, stream=None,
+           variant: str = "auto") -> None:
+    PackPlan.for_tensors(tensors, offsets).unpack(flat, tensors, scale, stream, variant)
 
 
 def make_hyper(lr: float, momentum: float = 0.0, dampening: float = 0.0, weight_decay: float = 0.0,

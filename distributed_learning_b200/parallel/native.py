@@ -8,10 +8,11 @@ rule -- with the machinery underneath replaced:
 reference                                    here
 ===========================================  =================================================
 tensor hook + spin on ``grad is None``       ``register_post_accumulate_grad_hook``
-sender thread: ``fuse`` (187 copies, D2H)    one ``dlb_pack`` launch per bucket on a side stream,
-                                             ordered after the bucket's last gradient by an event
-``reducer.put`` -> mp.Queue -> host sum      one allreduce kernel over NVLink peer memory
--> gloo ring -> mp.Queue                     (``csrc/allreduce.cu``), variant chosen per size
+sender thread: ``fuse`` (187 copies, D2H)    ONE kernel per bucket on a side stream, ordered after the
+``reducer.put`` -> mp.Queue -> host sum      bucket's last gradient by an event: its prologue gathers
+-> gloo ring -> mp.Queue                     the gradient tensors into the peer-mapped buffer, then it
+                                             all-reduces over NVLink peer memory
+                                             (``csrc/allreduce.cu``), variant chosen per size
 receiver thread: ``unfuse`` (187 copies)     ``.grad`` become views of the reduced buffer, or one
                                              ``dlb_unpack`` launch
 ``optimizer.step()`` (foreach SGD)           ``dlb_sgd_flat`` on the reduced buffer, or fused into
@@ -37,6 +38,7 @@ import torch
 import torch.nn as nn
 
 from ..ops import fused as F_ops
+from ..ops._lib import DLB_MAX_TENSORS
 from ..ops.comm import NativeComm, _round_up
 from ..utils.logging import Level, print_d
 from .buckets import Bucket, find_unused_parameters, fusion_grouping
@@ -67,6 +69,7 @@ class _NativeBucket:
         self.reduced: Optional[torch.Tensor] = None   # where this step's averaged gradient lives
         self.algo = "twoshot"
         self.nblocks = 16
+        self.unroll = 0
         self.sgd_done_in_kernel = False
 
     @property
@@ -80,13 +83,15 @@ class B200Dist(_Wrapper):
     def __init__(self, model, reducer=None, grouping_size: int = 25 * 1024 * 1024, grad_buff_device=None, *,
                  overlap: bool = True, algo: str = "auto", fused_sgd: bool = True, comm_dtype: str = "auto",
                  model_dtype: str = "fp32", cuda_graph: bool = False, group=None, comm: Optional[NativeComm] = None,
-                 exclude_unused: bool = True, unpack: str = "view", tune: bool = False, dynamic_unused: bool = False):
+                 exclude_unused: bool = True, unpack: str = "view", tune: bool = False, dynamic_unused: bool = False,
+                 fuse_pack: bool = True):
         super().__init__(model, reducer)
         d = self.__dict__
         d["grouping_size"] = int(grouping_size)
         d["overlap"] = bool(overlap)
         d["algo"] = algo
         d["fused_sgd"] = bool(fused_sgd)
+        d["fuse_pack"] = bool(fuse_pack) and not os.environ.get("DLB200_NO_FUSE_PACK")
         # dynamic_unused: the reference's behaviour (src/ourdist.py:137-172) -- walk the graph after
         # EVERY forward and hand a zero gradient to the parameters this step's loss does not reach,
         # so a model whose used-parameter set changes between steps still trains.  Every parameter
@@ -238,7 +243,7 @@ class B200Dist(_Wrapper):
             nb.regions = [self.comm.view(o, nb.numel, self.comm_dtype) for o in nb.region_offsets]
             nb.b.grad_buffer = nb.regions[0]
             if world > 1:
-                nb.algo, nb.nblocks = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
+                nb.algo, nb.nblocks, nb.unroll = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
             self._flatten_parameters(nb)
         d["buckets"] = buckets
         for nb in buckets:
@@ -255,9 +260,9 @@ class B200Dist(_Wrapper):
             sizes = sorted({nb.numel * esize for nb in buckets})
             self.comm.tune(sizes, self.comm_dtype)
             for nb in buckets:
-                nb.algo, nb.nblocks = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
+                nb.algo, nb.nblocks, nb.unroll = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
         print_d("B200Dist: " + ", ".join(f"bucket{nb.id}: {len(nb.tensors)} tensors {nb.numel * esize / 2**20:.2f} MiB "
-                                         f"{nb.algo}/{nb.nblocks}" for nb in buckets)
+                                         f"{nb.algo}/{nb.nblocks}" + (f"/u{nb.unroll}" if nb.algo == "nvls" else "") for nb in buckets)
                 + f" (arena {self.comm.mode}, multicast {'yes' if self.comm.has_multicast else 'no'}"
                 + (f": {self.comm.mc_note}" if self.comm.mc_note else "") + ")", Level.INFO)
 
@@ -314,20 +319,25 @@ class B200Dist(_Wrapper):
         src, dst = nb.regions[nb.cur], nb.regions[1 - nb.cur]
         opt = self.optimizer
         in_kernel = self.fused_sgd and opt is not None and world > 1
-        nb.plan.pack(src, grads, 1.0 / world, stream=cs)
-        launches = 1
+        # one kernel per bucket: the gather of the gradient tensors is the allreduce kernel's prologue
+        fuse = self.fuse_pack and world > 1 and len(nb.tensors) <= DLB_MAX_TENSORS
+        launches = 0
+        if not fuse:
+            nb.plan.pack(src, grads, 1.0 / world, stream=cs)
+            launches += 1
         if world > 1:
             sgd = None
             if in_kernel:
                 sgd = F_ops.fused_sgd_args(nb.master, nb.momentum, opt.hyper(), nb.shadow)
+            kw = dict(sgd=sgd, nblocks=nb.nblocks, stream=cs, unroll=nb.unroll)
+            if fuse:
+                kw.update(pack=nb.plan.bind(grads), pack_scale=1.0 / world)
             if nb.algo == "oneshot":
                 comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, "oneshot", 1.0,
-                               out_offset=nb.region_offsets[1 - nb.cur], sgd=sgd, nblocks=nb.nblocks, stream=cs,
-                               end_barrier=self.static_regions)
+                               out_offset=nb.region_offsets[1 - nb.cur], end_barrier=self.static_regions, **kw)
                 nb.reduced = dst
             else:
-                comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, nb.algo, 1.0, sgd=sgd,
-                               nblocks=nb.nblocks, stream=cs)
+                comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, nb.algo, 1.0, **kw)
                 nb.reduced = src
             launches += 1
         else:
@@ -607,10 +617,10 @@ class NativeReducer:
                     view[:n].copy_(flat)
                     if padded > n:
                         view[n:].zero_()
-                    algo, nblocks = comm.choose(padded * esize, buff.dtype, "auto")
+                    algo, nblocks, unroll = comm.choose(padded * esize, buff.dtype, "auto")
                     if algo == "oneshot":        # in place, and safe to refill right away
                         algo = "twoshot"
-                    comm.allreduce(0, padded, buff.dtype, algo, 1.0 / world, nblocks=nblocks, stream=self.stream)
+                    comm.allreduce(0, padded, buff.dtype, algo, 1.0 / world, nblocks=nblocks, stream=self.stream, unroll=unroll)
                     flat.copy_(view[:n])
                     self.launches += 1
                 done = torch.cuda.Event()

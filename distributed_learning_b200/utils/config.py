@@ -66,6 +66,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--algo", type=str, default="auto", choices=("auto", "oneshot", "twoshot", "nvls", "nvls_deep"),
                    help="native allreduce variant (auto: chosen per message size from measured bus bandwidth)")
     p.add_argument("--fused_sgd", type=int, default=1, help="b200 backend: apply SGD inside/after the allreduce kernel on the flat buffers")
+    p.add_argument("--fuse_pack", type=int, default=1, help="b200 backend: gather the gradients inside the allreduce kernel (one launch per bucket) instead of a separate pack launch")
     p.add_argument("--cuda_graph", type=int, default=0, help="b200 backend: capture the whole step in a CUDA graph")
     p.add_argument("--channels_last", type=int, default=0, help="NHWC weights and activations on the GPU")
     p.add_argument("--cudnn_benchmark", type=int, default=0, help="let cuDNN time its algorithms at the first step")

@@ -113,6 +113,17 @@ int dlb_pack(void* flat, int flat_dtype, void* const* tensors, const int* tensor
              const int64_t* offsets, const int64_t* numels, int ntensors, float scale, void* stream);
 int dlb_unpack(const void* flat, int flat_dtype, void* const* tensors, const int* tensor_dtypes,
                const int64_t* offsets, const int64_t* numels, int ntensors, float scale, void* stream);
+/* The same with the kernel named: 0 = pick (what dlb_pack does), 1 = "chunks" (one CTA per 8192
+ * elements of one tensor; any layout), 2 = "tiles" (persistent CTAs over equal tiles of the flat
+ * buffer, owner of each 16-byte vector looked up in shared memory), 3 = "bulk" (cp.async.bulk +
+ * mbarrier through a shared-memory ring; tensor dtype must equal the flat dtype).  2 and 3 need a
+ * vector-aligned layout: ascending non-overlapping offsets, each a multiple of 16 bytes of the flat
+ * dtype, and a flat buffer that extends to the next 16-byte boundary after its last tensor (the pad
+ * elements are written as zeros by pack). */
+int dlb_pack_ex(void* flat, int flat_dtype, void* const* tensors, const int* tensor_dtypes, const int64_t* offsets,
+                const int64_t* numels, int ntensors, float scale, int variant, void* stream);
+int dlb_unpack_ex(const void* flat, int flat_dtype, void* const* tensors, const int* tensor_dtypes, const int64_t* offsets,
+                  const int64_t* numels, int ntensors, float scale, int variant, void* stream);
 
 /* ---- K-sgd (reference optim.SGD(lr=0.01, momentum=0.5), src/main.py:36,91) -------------------
  * buf = momentum*buf + (1-dampening)*(g*grad_scale + weight_decay*p);  p -= lr*(nesterov ? g'+momentum*buf : buf)
@@ -164,11 +175,55 @@ int dlb_allreduce_oneshot(void* const* bufs, void* out, void* const* sigs, uint3
 int dlb_allreduce_nvls(void* mc_buf, void* const* bufs, void* const* sigs, uint32_t* state, int rank, int nranks,
                        int64_t numel, int dtype, float scale, int nblocks, int nthreads,
                        const dlb_fused_sgd_t* sgd, void* stream);
-/* EXPERIMENTAL, not selected by default and not yet measured on hardware: dlb_allreduce_nvls with
- * eight multimem.ld_reduce in flight per thread instead of two (same arguments, same result). */
+/* dlb_allreduce_nvls with eight multimem.ld_reduce in flight per thread instead of four (same
+ * arguments, same result; dlb_allreduce's `unroll`). */
 int dlb_allreduce_nvls_deep(void* mc_buf, void* const* bufs, void* const* sigs, uint32_t* state, int rank, int nranks,
                             int64_t numel, int dtype, float scale, int nblocks, int nthreads,
                             const dlb_fused_sgd_t* sgd, void* stream);
+/* The general form: everything above plus the FUSED PACK PROLOGUE, the unroll of the nvls variant
+ * and the phase trace, in one descriptor (zero-initialise it, then set what you need).
+ *   tensors/tensor_dtypes/offsets/numels/ntensors  when ntensors > 0 the kernel first gathers the
+ *           bucket's gradient tensors into bufs[rank] (flat[offset_i + k] = cast(tensor_i[k] *
+ *           pack_scale); a NULL tensor packs zeros), each CTA packing exactly the tiles its peers'
+ *           same-numbered CTAs will pull, then runs the entry barrier: one launch per bucket
+ *           instead of dlb_pack + allreduce (reference Group.fuse, src/ourdist.py:28-36, followed
+ *           by the reducer).  Needs the vector-aligned layout of dlb_pack_ex and at most
+ *           DLB_MAX_TENSORS tensors.
+ *   unroll  nvls only: switch reductions in flight per thread, 2 / 4 / 8 (0 = 4).  Every rank must
+ *           pass the same value (it sets the tile that CTAs own).
+ *   trace   optional device pointer to 8 uint64: %globaltimer (ns) of CTA 0 at start, packed, entry
+ *           barrier passed, data phase done, exit barrier passed, epilogue done. */
+enum { DLB_ALGO_TWOSHOT = 0, DLB_ALGO_ONESHOT = 1, DLB_ALGO_NVLS = 2 };
+
+typedef struct {
+    int algo, rank, nranks;
+    void* const* bufs;
+    void* out;    /* one-shot */
+    void* mc_buf; /* nvls */
+    void* const* sigs;
+    uint32_t* state;
+    int64_t numel;
+    int dtype;
+    float scale;
+    int nblocks, nthreads, unroll, end_barrier;
+    const dlb_fused_sgd_t* sgd;
+    void* const* tensors;
+    const int* tensor_dtypes;
+    const int64_t* offsets;
+    const int64_t* numels;
+    int ntensors;
+    float pack_scale; /* 0 is read as 1 */
+    unsigned long long* trace;
+} dlb_allreduce_desc_t;
+
+int dlb_allreduce(const dlb_allreduce_desc_t* desc, void* stream);
+
+/* Every rank copies `nbytes` (multiple of 16) of bufs[root] into its own bufs[rank]; two barriers, so
+ * the root may refill its buffer as soon as the kernel is done.  Gives every replica rank 0's initial
+ * parameters without another communication library (the reference relies on equal seeds,
+ * src/main.py:31-34). */
+int dlb_broadcast(void* const* bufs, void* const* sigs, uint32_t* state, int rank, int nranks, int root, int64_t nbytes,
+                  int nblocks, int nthreads, void* stream);
 /* device-side barrier on its own (used at bring-up and by tests) */
 int dlb_barrier(void* const* sigs, uint32_t* state, int rank, int nranks, int nblocks, void* stream);
 /* spin budget of the device-side waits in milliseconds (default 600000, or $DLB200_WAIT_TIMEOUT_MS; 0 = wait forever) */
@@ -185,6 +240,27 @@ int dlb_comm_check(uint32_t* state, void* stream);
 int dlb_allreduce_emulated(int algo, void* const* bufs, void* const* outs, const dlb_fused_sgd_t* sgds, void* flags,
                            int nranks, int64_t numel, int dtype, float scale, int nblocks, int nthreads, void* stream);
 size_t dlb_emulated_flags_bytes(int nranks);
+/* The emulation in descriptor form, with the fused pack prologue: tensor i of emulated rank r is
+ * read at tensors[i] + r * numels[i] * sizeof(dtype_i), i.e. each tensor is stored as [nranks, numel]. */
+typedef struct {
+    int algo, nranks;
+    void* const* bufs;
+    void* const* outs;
+    const dlb_fused_sgd_t* sgds;
+    void* flags;
+    int64_t numel;
+    int dtype;
+    float scale;
+    int nblocks, nthreads;
+    void* const* tensors;
+    const int* tensor_dtypes;
+    const int64_t* offsets;
+    const int64_t* numels;
+    int ntensors;
+    float pack_scale;
+    unsigned long long* trace; /* 8 uint64 per emulated rank */
+} dlb_emulated_desc_t;
+int dlb_allreduce_emulated_ex(const dlb_emulated_desc_t* desc, void* stream);
 
 /* dlb_allreduce_emulated without the caller-provided scratch, for callers that cannot allocate
  * device memory (a plug-in inside a process whose allocator it does not own, a self-test on a

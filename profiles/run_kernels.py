@@ -20,6 +20,7 @@ from distributed_learning_b200.parallel.buckets import Bucket  # noqa: E402
 
 
 ONCE = "--once" in sys.argv      # one launch per kernel: the mode captured under ncu
+VARIANTS = ("chunks", "tiles", "bulk")
 
 
 def timed(fn, iters=20, flush=None):
@@ -52,23 +53,47 @@ def main():
     hbm = float(peaks.get("hbm_gbs", 6650.0))
     flush = torch.zeros(128 << 20, device=dev)
     out = {"hbm_gbs_denominator": hbm, "denominator_source": "measured" if peaks else "fallback", "kernels": {}}
+    from bench import ClockSampler  # noqa: E402
 
-    # ---- K-pack / K-unpack on GoogLeNet's gradient list -------------------------------------------
+    clocks = ClockSampler(0).start()
+
+    # ---- K-pack / K-unpack on the gradient lists of GoogLeNet (one bucket) and ResNet-50 ---------------
+    from distributed_learning_b200.models import ResNet50  # noqa: E402
+
     with torch.device("meta"):
-        net = GoogLeNet()
-    shapes = [p.shape for n, p in net.named_parameters() if not n.startswith(("model.aux1", "model.aux2"))]
-    grads = [torch.randn(s, device=dev) for s in reversed(shapes)]
-    b = Bucket(0, grads, aligned=True, allocate=False)
-    plan = K.PackPlan.for_tensors(grads, b.offsets)
-    for name, dt in (("fp32", torch.float32), ("bf16", torch.bfloat16)):
-        flat = torch.zeros(b.numel, device=dev, dtype=dt)
-        nbytes = b.dense_numel * (4 + flat.element_size())
-        us = timed(lambda: plan.pack(flat, grads, 0.125), flush=flush)
-        out["kernels"][f"pack_googlenet_173t_to_{name}"] = {"us": us, "bytes": nbytes, "GBs": nbytes / us / 1e3,
-                                                            "frac_hbm": nbytes / us / 1e3 / hbm}
-        us = timed(lambda: plan.unpack(flat, grads, 1.0), flush=flush)
-        out["kernels"][f"unpack_googlenet_173t_from_{name}"] = {"us": us, "bytes": nbytes, "GBs": nbytes / us / 1e3,
-                                                                "frac_hbm": nbytes / us / 1e3 / hbm}
+        nets = {"googlenet_173t": [p.shape for n, p in GoogLeNet().named_parameters()
+                                   if not n.startswith(("model.aux1", "model.aux2"))],
+                "resnet50_161t": [p.shape for p in ResNet50().parameters()]}
+    for net_name, shapes in nets.items():
+        for name, dt in (("fp32", torch.float32), ("bf16", torch.bfloat16)):
+            # tensors in the flat dtype (what the training path packs: fp32 grads -> fp32 bucket, bf16 -> bf16)
+            grads = [torch.randn(s, device=dev).to(dt) for s in reversed(shapes)]
+            b = Bucket(0, grads, dtype=dt, aligned=True, allocate=False)
+            plan = K.PackPlan.for_tensors(grads, b.offsets)
+            flat = torch.zeros(b.numel, device=dev, dtype=dt)
+            nbytes = b.dense_numel * 2 * flat.element_size()
+            for variant in VARIANTS:
+                for scale in (1.0, 0.125):
+                    tag = f"{net_name}_{name}_{variant}" + ("" if scale == 1.0 else "_scaled")
+                    us = timed(lambda: plan.pack(flat, grads, scale, variant=variant), flush=flush)
+                    out["kernels"][f"pack_{tag}"] = {"us": us, "bytes": nbytes, "GBs": nbytes / us / 1e3,
+                                                     "frac_hbm": nbytes / us / 1e3 / hbm}
+                us = timed(lambda: plan.unpack(flat, grads, 1.0, variant=variant), flush=flush)
+                out["kernels"][f"unpack_{net_name}_{name}_{variant}"] = {"us": us, "bytes": nbytes, "GBs": nbytes / us / 1e3,
+                                                                          "frac_hbm": nbytes / us / 1e3 / hbm}
+        # mixed: fp32 gradients into a bf16 bucket (comm_dtype bf16 on an fp32 model) -- conversion in flight
+        grads = [torch.randn(s, device=dev) for s in reversed(shapes)]
+        b = Bucket(0, grads, dtype=torch.bfloat16, aligned=True, allocate=False)
+        plan = K.PackPlan.for_tensors(grads, b.offsets)
+        flat = torch.zeros(b.numel, device=dev, dtype=torch.bfloat16)
+        nbytes = b.dense_numel * 6
+        for variant in ("chunks", "tiles"):
+            us = timed(lambda: plan.pack(flat, grads, 0.125, variant=variant), flush=flush)
+            out["kernels"][f"pack_{net_name}_fp32_to_bf16_{variant}"] = {"us": us, "bytes": nbytes, "GBs": nbytes / us / 1e3,
+                                                                       "frac_hbm": nbytes / us / 1e3 / hbm}
+            us = timed(lambda: plan.unpack(flat, grads, 1.0, variant=variant), flush=flush)
+            out["kernels"][f"unpack_{net_name}_bf16_to_fp32_{variant}"] = {"us": us, "bytes": nbytes, "GBs": nbytes / us / 1e3,
+                                                                         "frac_hbm": nbytes / us / 1e3 / hbm}
 
     # ---- K-sgd on 64 MiB ---------------------------------------------------------------------------------
     n = 16 << 20
@@ -94,6 +119,7 @@ def main():
         us = timed(lambda: C.emulated_allreduce(bufs, scale=0.25, flags=flags, nblocks=32, nthreads=512, **kw), flush=flush)
         out["kernels"][f"allreduce_emulated_4x16MiB_{name}"] = {"us": us, "note": "single GPU: HBM stands in for NVLink"}
     del keep
+    out["clocks"] = clocks.stop()
     print(json.dumps(out))
 
 

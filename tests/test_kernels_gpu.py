@@ -18,30 +18,55 @@ def _layout(sizes, esize):
     return offs, cur
 
 
+@pytest.mark.parametrize("variant", ["auto", "chunks", "tiles", "bulk"])
 @pytest.mark.parametrize("flat_dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("src_dtype", [torch.float32, torch.bfloat16, torch.float16])
-def test_pack_unpack_matches_torch(flat_dtype, src_dtype):
+def test_pack_unpack_matches_torch(flat_dtype, src_dtype, variant):
     from distributed_learning_b200.ops import fused as K
 
+    if variant == "bulk" and src_dtype != flat_dtype:
+        pytest.skip("the bulk-copy variant moves bytes: same dtype on both sides")
     dev = _dev()
     torch.manual_seed(0)
     sizes = [1, 3, 7, 8, 64, 1000, 8191, 8192, 8193, 100003, 300000]
     tensors = [torch.randn(n, device=dev).to(src_dtype) for n in sizes]
     offs, total = _layout(sizes, torch.empty((), dtype=flat_dtype).element_size())
-    flat = torch.full((total,), 7.0, device=dev, dtype=flat_dtype)
-    scale = 0.125
-    K.pack(flat, tensors, offs, scale=scale)
+    for scale in (0.125, 1.0):
+        flat = torch.full((total,), 7.0, device=dev, dtype=flat_dtype)
+        K.pack(flat, tensors, offs, scale=scale, variant=variant)
+        torch.cuda.synchronize()
+        for t, o in zip(tensors, offs):
+            want = (t.float() * scale).to(flat_dtype)
+            assert torch.equal(flat[o:o + t.numel()], want), (t.numel(), scale)
+        # unpack into fresh tensors (cast back, scale 1/scale)
+        back = [torch.zeros_like(t) for t in tensors]
+        K.unpack(flat, back, offs, scale=1.0 / scale, variant=variant)
+        torch.cuda.synchronize()
+        for t, b, o in zip(tensors, back, offs):
+            want = (flat[o:o + t.numel()].float() / scale).to(src_dtype)
+            assert torch.equal(b, want), (t.numel(), scale)
+
+
+@pytest.mark.parametrize("variant", ["tiles", "bulk"])
+def test_pack_variants_leave_holes_alone_and_zero_the_pads(variant):
+    """Layout with holes between tensors and with storage that is not 16-byte aligned."""
+    from distributed_learning_b200.ops import fused as K
+
+    dev = _dev()
+    torch.manual_seed(5)
+    base = torch.randn(70000, device=dev)
+    a, b, c = base[:5001], base[5001:5001 + 20000], torch.randn(9, device=dev)     # b's storage is misaligned
+    offs = [0, 8192, 40960]                # a: 0..5001 (+pad to 5004), hole, b, hole, c
+    flat = torch.full((41000,), 7.0, device=dev)
+    K.pack(flat, [a, b, c], offs, scale=1.0, variant=variant)
     torch.cuda.synchronize()
-    for t, o in zip(tensors, offs):
-        want = (t.float() * scale).to(flat_dtype)
-        assert torch.equal(flat[o:o + t.numel()], want)
-    # unpack into fresh tensors (cast back, scale 1/scale)
-    back = [torch.zeros_like(t) for t in tensors]
-    K.unpack(flat, back, offs, scale=1.0 / scale)
+    assert torch.equal(flat[:5001], a) and torch.equal(flat[8192:28192], b) and torch.equal(flat[40960:40969], c)
+    assert torch.count_nonzero(flat[5001:5004]) == 0 and torch.count_nonzero(flat[40969:40972]) == 0
+    assert torch.all(flat[5004:8192] == 7.0) and torch.all(flat[28192:40960] == 7.0) and torch.all(flat[40972:] == 7.0)
+    back = [torch.zeros_like(t) for t in (a, b, c)]
+    K.unpack(flat, back, offs, variant=variant)
     torch.cuda.synchronize()
-    for t, b, o in zip(tensors, back, offs):
-        want = (flat[o:o + t.numel()].float() / scale).to(src_dtype)
-        assert torch.equal(b, want)
+    assert all(torch.equal(x, y) for x, y in zip(back, (a, b, c)))
 
 
 def test_pack_none_tensor_and_unaligned_views_and_many_tensors():
