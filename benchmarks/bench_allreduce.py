@@ -67,6 +67,9 @@ def main():
     ap.add_argument("--factor", type=int, default=4)
     ap.add_argument("--dtype", default="fp32", choices=("fp32", "bf16"))
     ap.add_argument("--blocks", default="8,16,32,48,64")
+    ap.add_argument("--unrolls", default="4,8", help="nvls pipeline depths to try (2, 4, 8)")
+    ap.add_argument("--algos", default=None, help="comma list; default: every variant the box supports")
+    ap.add_argument("--no-nccl", action="store_true", help="skip the NCCL comparison rows")
     ap.add_argument("--ring", action="store_true", help="also time the reference-style host-driven NCCL send/recv ring")
     ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays of the launches (device-side time, no host launch cost)")
     ap.add_argument("--out", default=None)
@@ -87,15 +90,22 @@ def main():
     if rank == 0:
         print(f"arena {comm.mode}, multicast {comm.has_multicast} {comm.mc_note}", flush=True)
     blocks = [int(b) for b in args.blocks.split(",")]
+    unrolls = [int(u) for u in args.unrolls.split(",")]
     algos = ["oneshot", "twoshot"] + (["nvls"] if comm.has_multicast else [])
-    if comm.has_multicast and os.environ.get("DLB200_EXPERIMENTAL"):
-        algos.append("nvls_deep")
+    if args.algos:
+        algos = [a for a in args.algos.split(",") if a != "nvls" or comm.has_multicast]
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from bench import ClockSampler
+
+    clocks = ClockSampler(device.index).start()
+    trace = torch.zeros(8, dtype=torch.int64, device=device)
     rows = []
     size = args.min_bytes
     while size <= args.max_bytes:
         numel = size // esize
         iters = 200 if size <= 1 << 20 else (50 if size <= 64 << 20 else 10)
         row = {"bytes": size, "ms": {}, "best": None}
+        runners = {}
         comm.view(0, numel, dtype).normal_()
         comm.view(region, numel, dtype).normal_()
         for algo in algos:
@@ -104,17 +114,24 @@ def main():
             for nb in blocks:
                 if size <= 64 << 10 and nb > 16:
                     continue
-                flip = [0]
+                for un in (unrolls if algo == "nvls" else [0]):
+                    if algo == "nvls" and size // world <= 512 * 16 * 2 * nb and un > min(unrolls):
+                        continue        # one tile per CTA already covers the slice: deeper unroll changes nothing
+                    flip = [0]
 
-                def run(algo=algo, nb=nb):
-                    a, b = (0, region) if flip[0] == 0 else (region, 0)
-                    flip[0] ^= 1
-                    comm.allreduce(a, numel, dtype, algo, scale=1.0 / world, out_offset=b, nblocks=nb,
-                                   stream=torch.cuda.current_stream(device))
+                    def run(algo=algo, nb=nb, un=un, tr=None):
+                        a, b = (0, region) if flip[0] == 0 else (region, 0)
+                        flip[0] ^= 1
+                        comm.allreduce(a, numel, dtype, algo, scale=1.0 / world, out_offset=b, nblocks=nb,
+                                       stream=torch.cuda.current_stream(device), unroll=un, trace=tr)
 
-                row["ms"][f"{algo}/{nb}"] = timed(run, 5, iters, device, args.graph)
+                    row["ms"][f"{algo}/{nb}" + (f"/u{un}" if un else "")] = timed(run, 5, iters, device, args.graph)
+                    runners[f"{algo}/{nb}" + (f"/u{un}" if un else "")] = run
         x = torch.randn(numel, device=device).to(dtype)
-        row["ms"]["nccl"] = timed(lambda: dist.all_reduce(x), 5, iters, device, args.graph)
+        if args.no_nccl:
+            row["ms"]["nccl"] = float("nan")
+        else:
+            row["ms"]["nccl"] = timed(lambda: dist.all_reduce(x), 5, iters, device, args.graph)
         if args.ring and size >= 4096:
             row["ms"]["nccl_ring_hostdriven"] = timed(lambda: ring_allreduce_gpu(x), 2, max(2, iters // 10), device)
         native = {k: v for k, v in row["ms"].items() if not k.startswith("nccl")}
@@ -127,14 +144,22 @@ def main():
         row["frac_of_900"] = row["busbw_GBs"] / 900.0
         row["frac_of_770_measured_copy"] = row["busbw_GBs"] / 770.0
         row["speedup_vs_nccl"] = row["ms"]["nccl"] / native[best]
+        # where the time of the best variant goes: %globaltimer at the phase boundaries of CTA 0, rank 0
+        dist.barrier()
+        runners[best](tr=trace)
+        torch.cuda.synchronize(device)
+        t = trace.cpu().tolist()
+        row["phases_us_rank0"] = {k: (t[i + 1] - t[i]) / 1000.0 for i, k in
+                                  enumerate(("pack", "entry_barrier", "data", "exit_barrier", "epilogue"))}
         rows.append(row)
         if rank == 0:
-            print(f"{size:>11d} B  best {best:<12s} {native[best] * 1000:9.1f} us  busbw {row['busbw_GBs']:7.1f} GB/s "
+            print(f"{size:>11d} B  best {best:<14s} {native[best] * 1000:9.1f} us  busbw {row['busbw_GBs']:7.1f} GB/s "
                   f"({row['frac_of_900'] * 100:5.1f}% of 900)  nccl {row['ms']['nccl'] * 1000:9.1f} us "
                   f"{row['nccl_busbw_GBs']:7.1f} GB/s  x{row['speedup_vs_nccl']:.2f}", flush=True)
         size *= args.factor
     comm.check()
     result = {"n_gpus": world, "dtype": args.dtype, "arena": comm.mode, "multicast": comm.has_multicast,
+              "clocks": clocks.stop(),
               "timing": ("CUDA events around one CUDA-graph replay of the launches" if args.graph else
                          "CUDA events, back-to-back launches") + ", max over ranks", "rows": rows}
     if rank == 0 and args.out:

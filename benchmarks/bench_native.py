@@ -50,7 +50,6 @@ def _timed(batches, k, device, clocks=None, comm=None):
 def run(args, helpers) -> dict:
     from distributed_learning_b200.models import create_network
     from distributed_learning_b200.parallel.native import B200Dist
-    from distributed_learning_b200.trainer import broadcast_initial_state
     from distributed_learning_b200.utils.data import INPUT_SPECS, NativeHostRandom, PinnedPrefetcher
 
     rank, local_rank, world = helpers.dist_env()
@@ -72,7 +71,6 @@ def run(args, helpers) -> dict:
     if args.channels_last:
         model = model.to(memory_format=torch.channels_last)
     model.train()
-    broadcast_initial_state(model)          # before wrapping: the wrapper re-homes the parameters
     wrapper = B200Dist(model, None, args.grouping_size, device, overlap=bool(args.overlap), algo=args.algo,
                        fused_sgd=bool(args.fused_sgd), fuse_pack=bool(args.fuse_pack), model_dtype=dtype, tune=bool(args.tune),
                        cuda_graph=bool(args.cuda_graph))

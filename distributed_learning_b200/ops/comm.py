@@ -427,6 +427,52 @@ class NativeComm:
                                   nbytes, nblocks, self.nthreads, stream_handle(stream)))
         self.launches += 1
 
+    def broadcast_tensors(self, tensors: Sequence[torch.Tensor], root: int = 0) -> int:
+        """Collective.  Overwrite every tensor in ``tensors`` (same shapes and dtypes on all ranks) with
+        ``root``'s values, staging through the arena's data area: local copy in, one ``broadcast``
+        kernel, local copy out.  The arena's contents are destroyed.  Returns the bytes moved."""
+        if self.world == 1 or not tensors:
+            return 0
+        cap = (self.nbytes - self.data_offset) // 16 * 16
+        stage = self.local[self.data_offset:self.data_offset + cap]
+        moved = 0
+        pending: List[Tuple[torch.Tensor, int, int]] = []      # (destination bytes, offset in the stage, count)
+
+        def flush(used: int) -> None:
+            self.broadcast(0, _round_up(used, 16), root=root)
+            for dst, off, n in pending:
+                dst.copy_(stage[off:off + n])
+            pending.clear()
+
+        used = 0
+        with torch.no_grad():
+            for t in tensors:
+                flat = t.detach().contiguous().view(-1).view(torch.uint8)     # a copy when t is not contiguous
+                done = 0
+                while done < flat.numel():
+                    if used == cap:
+                        flush(used)
+                        used = 0
+                    n = min(flat.numel() - done, cap - used)
+                    piece = flat[done:done + n]
+                    stage[used:used + n].copy_(piece)
+                    pending.append((piece, used, n))
+                    used = _round_up(used + n, 16) if used + n < cap else cap
+                    done += n
+                    moved += n
+                    if used >= cap:
+                        flush(cap)
+                        used = 0
+                if flat.data_ptr() != t.data_ptr():
+                    # the staging copy was filled above only after the flush; write back through it
+                    if pending:
+                        flush(used)
+                        used = 0
+                    t.detach().copy_(flat.view(t.dtype).view(t.shape))
+            if pending:
+                flush(used)
+        return moved
+
     def barrier(self, stream=None, nblocks: int = 1) -> None:
         check(lib().dlb_barrier(self._sig_array, self.state.data_ptr(), self.rank, self.world, nblocks, stream_handle(stream)))
         self.launches += 1

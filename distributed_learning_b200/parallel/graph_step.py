@@ -14,8 +14,9 @@ nothing: N calls make exactly N updates, as in eager mode (``tests/test_graph_pa
 
 Constraints (checked or documented): static shapes; the learning rate and momentum are baked
 into the captured kernels (re-capture after changing them); the wrapper must be built with
-``cuda_graph=True`` so every step uses the same arena regions and the one-shot variant keeps its
-trailing barrier; all ranks must replay the same number of times.
+``cuda_graph=True``; two graphs are captured, one per arena-region parity, and replayed
+alternately (so the one-shot variant keeps the region alternation that spares it a trailing
+barrier); all ranks must replay the same number of times.
 """
 from __future__ import annotations
 
@@ -57,6 +58,21 @@ class GraphedTrainStep:
         with torch.cuda.graph(self.graph):
             self.loss = self._eager()
         self.launches_per_step = getattr(wrapper, "kernel_launches", 0) - before
+        # Second graph with the buckets' other arena regions: replayed on odd steps, so consecutive
+        # steps alternate regions exactly as eager mode does and the one-shot variant needs no
+        # trailing barrier.  Both graphs share one memory pool (they never run concurrently).
+        self.graphs = [self.graph]
+        self.losses = [self.loss]
+        if getattr(wrapper, "alternate_graphs", False):
+            wrapper.__dict__["graph_parity"] = 1
+            g1 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g1, pool=self.graph.pool()):
+                l1 = self._eager()
+            wrapper.__dict__["graph_parity"] = 0
+            wrapper.__dict__["kernel_launches"] = before + self.launches_per_step
+            self.graphs.append(g1)
+            self.losses.append(l1)
+        self.calls = 0
         if snap is not None:
             torch.cuda.synchronize(dev)
             wrapper.restore_state(snap)
@@ -77,7 +93,10 @@ class GraphedTrainStep:
             self.data.copy_(data, non_blocking=True)
         if target.data_ptr() != self.target.data_ptr():
             self.target.copy_(target, non_blocking=True)
-        self.graph.replay()
+        k = self.calls % len(self.graphs)
+        self.calls += 1
+        self.graphs[k].replay()
+        self.loss = self.losses[k]
         if hasattr(self.optimizer, "steps"):
             self.optimizer.steps += 1           # the replay ran the update; no Python optimizer code did
         if hasattr(self.wrapper, "kernel_launches"):

@@ -84,7 +84,7 @@ class B200Dist(_Wrapper):
                  overlap: bool = True, algo: str = "auto", fused_sgd: bool = True, comm_dtype: str = "auto",
                  model_dtype: str = "fp32", cuda_graph: bool = False, group=None, comm: Optional[NativeComm] = None,
                  exclude_unused: bool = True, unpack: str = "view", tune: bool = False, dynamic_unused: bool = False,
-                 fuse_pack: bool = True):
+                 fuse_pack: bool = True, sync_initial_state: bool = True, comm_kernel_when_alone: bool = False):
         super().__init__(model, reducer)
         d = self.__dict__
         d["grouping_size"] = int(grouping_size)
@@ -92,6 +92,13 @@ class B200Dist(_Wrapper):
         d["algo"] = algo
         d["fused_sgd"] = bool(fused_sgd)
         d["fuse_pack"] = bool(fuse_pack) and not os.environ.get("DLB200_NO_FUSE_PACK")
+        # every replica starts from rank 0's parameters and buffers, copied by the
+        # native broadcast kernel once the flat buffers exist -- no other communication library
+        d["sync_initial_state"] = bool(sync_initial_state)
+        # a world of one normally skips the communication kernel (pack, then the flat SGD kernel);
+        # with this flag it launches the same fused kernel a multi-GPU job does, with nranks = 1, so
+        # the whole gradient path (pack prologue, barrier, reduce, SGD epilogue) runs on a single GPU
+        d["comm_kernel_when_alone"] = bool(comm_kernel_when_alone) or bool(os.environ.get("DLB200_COMM_KERNEL_WHEN_ALONE"))
         # dynamic_unused: the reference's behaviour (src/ourdist.py:137-172) -- walk the graph after
         # EVERY forward and hand a zero gradient to the parameters this step's loss does not reach,
         # so a model whose used-parameter set changes between steps still trains.  Every parameter
@@ -122,7 +129,12 @@ class B200Dist(_Wrapper):
         d["optimizer"] = None
         d["_fp32_stash"] = None
         d["kernel_launches"] = 0
-        d["static_regions"] = bool(cuda_graph)   # graph replay reuses the captured region every step
+        # under a CUDA graph the regions cannot flip per step from Python; GraphedTrainStep captures
+        # TWO graphs, one per region parity (`graph_parity`), and replays them alternately, so the
+        # one-shot variant keeps the alternation that spares it a trailing barrier
+        d["static_regions"] = bool(cuda_graph)
+        d["graph_parity"] = 0
+        d["alternate_graphs"] = bool(cuda_graph) and not os.environ.get("DLB200_SINGLE_GRAPH")
         d["nvtx"] = bool(int(os.environ.get("DLB200_NVTX", "0")))
         if d["model_dtype"] == torch.bfloat16:
             self._convert_to_bf16()
@@ -242,10 +254,16 @@ class B200Dist(_Wrapper):
         for nb in buckets:
             nb.regions = [self.comm.view(o, nb.numel, self.comm_dtype) for o in nb.region_offsets]
             nb.b.grad_buffer = nb.regions[0]
-            if world > 1:
+            if world > 1 or self.comm_kernel_when_alone:
                 nb.algo, nb.nblocks, nb.unroll = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
             self._flatten_parameters(nb)
         d["buckets"] = buckets
+        if world > 1 and self.sync_initial_state:
+            flats = [nb.master for nb in buckets] + [nb.shadow for nb in buckets if nb.shadow is not None]
+            bucketed = {id(t) for nb in buckets for t in nb.tensors}
+            rest = [p for p in self.model.parameters() if id(p) not in bucketed] + list(self.model.buffers())
+            moved = self.comm.broadcast_tensors(flats + rest, root=0)
+            print_d(f"B200Dist: initial state broadcast from rank 0 by the native kernel ({moved / 2**20:.1f} MiB)", Level.DEBUG)
         for nb in buckets:
             for t in nb.tensors:
                 self._hooks.append(t.register_post_accumulate_grad_hook(self._make_hook(nb)))
@@ -316,16 +334,19 @@ class B200Dist(_Wrapper):
         cs.wait_event(ready)
         grads = [t.grad for t in nb.tensors]
         self._held.append(grads)              # keep the memory alive until the compute stream has waited for us
+        if self.static_regions:
+            nb.cur = self.graph_parity if self.alternate_graphs else 0
         src, dst = nb.regions[nb.cur], nb.regions[1 - nb.cur]
         opt = self.optimizer
-        in_kernel = self.fused_sgd and opt is not None and world > 1
+        use_comm = world > 1 or self.comm_kernel_when_alone
+        in_kernel = self.fused_sgd and opt is not None and use_comm
         # one kernel per bucket: the gather of the gradient tensors is the allreduce kernel's prologue
-        fuse = self.fuse_pack and world > 1 and len(nb.tensors) <= DLB_MAX_TENSORS
+        fuse = self.fuse_pack and use_comm and len(nb.tensors) <= DLB_MAX_TENSORS
         launches = 0
         if not fuse:
             nb.plan.pack(src, grads, 1.0 / world, stream=cs)
             launches += 1
-        if world > 1:
+        if use_comm:
             sgd = None
             if in_kernel:
                 sgd = F_ops.fused_sgd_args(nb.master, nb.momentum, opt.hyper(), nb.shadow)
@@ -334,7 +355,8 @@ class B200Dist(_Wrapper):
                 kw.update(pack=nb.plan.bind(grads), pack_scale=1.0 / world)
             if nb.algo == "oneshot":
                 comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, "oneshot", 1.0,
-                               out_offset=nb.region_offsets[1 - nb.cur], end_barrier=self.static_regions, **kw)
+                               out_offset=nb.region_offsets[1 - nb.cur],
+                               end_barrier=self.static_regions and not self.alternate_graphs, **kw)
                 nb.reduced = dst
             else:
                 comm.allreduce(nb.region_offsets[nb.cur], nb.numel, nb.comm_dtype, nb.algo, 1.0, **kw)

@@ -88,8 +88,9 @@ def worker_process(node_id: int, worker_id: int, config, reducer, gpu_reduce: bo
     model = prepare_model(config, device)
     resuming = bool(getattr(config, "checkpoint", None) and getattr(config, "resume", 0)
                     and os.path.exists(config.checkpoint))
-    if not resuming:
-        # before wrapping: the native wrapper re-homes the parameters in flat buffers
+    if not resuming and getattr(config, "backend", "gloo") != "b200":
+        # host-driven backends: through the process group, before wrapping.  The native wrapper does
+        # it itself with its broadcast kernel once its flat buffers exist (B200Dist._build)
         broadcast_initial_state(model, getattr(config, "worker_group", None))
     buff_device = device if gpu_reduce else "cpu"
     model = config.distribute_model(model, reducer, config.grouping_size, buff_device)

@@ -22,9 +22,7 @@ def gathered_sum(x, world, scale, dtype):
 def check_allreduce(comm, rank, world, dev):
     from distributed_learning_b200.ops import fused as K
 
-    algos = ["twoshot", "oneshot"] + (["nvls"] if comm.has_multicast else [])
-    if comm.has_multicast and os.environ.get("DLB200_EXPERIMENTAL"):
-        algos.append("nvls_deep")
+    algos = ["twoshot", "oneshot"] + (["nvls", "nvls_u2", "nvls_u8"] if comm.has_multicast else [])
     for dtype in (torch.float32, torch.bfloat16):
         esize = 4 if dtype == torch.float32 else 2
         for numel in (16, 4096, 100000 // 8 * 8, 1 << 22):
@@ -36,11 +34,14 @@ def check_allreduce(comm, rank, world, dev):
                     buf = comm.view(0, numel, dtype)
                     buf.copy_(x)
                     out_off = (numel * esize + 4095) // 4096 * 4096
-                    comm.allreduce(0, numel, dtype, algo, scale=1.0 / world, out_offset=out_off)
+                    name, _, un = algo.partition("_u")
+                    comm.allreduce(0, numel, dtype, name, scale=1.0 / world, out_offset=out_off, unroll=int(un or 0))
                     res = comm.view(out_off, numel, dtype) if algo == "oneshot" else buf
                     torch.cuda.synchronize()
                     if algo.startswith("nvls"):
-                        ok = torch.allclose(res.float(), want.float(), rtol=2e-2 if esize == 2 else 1e-5, atol=1e-2 if esize == 2 else 1e-5)
+                        # the switch sums in fp32 in an order of its own; for bf16 it rounds the sum to
+                        # bf16 before the kernel scales and rounds again: one bf16 ulp (2^-8 relative)
+                        ok = torch.allclose(res.float(), want.float(), rtol=8e-3 if esize == 2 else 1e-5, atol=1e-5)
                     else:
                         ok = torch.equal(res, want)
                     if not ok:
@@ -50,6 +51,7 @@ def check_allreduce(comm, rank, world, dev):
     # fused SGD epilogue
     numel = 1 << 18
     h = K.make_hyper(0.01, 0.5)
+    algos = [a for a in algos if "_u" not in a]
     for algo in algos:
         p = torch.ones(numel, device=dev)
         m = torch.zeros(numel, device=dev)
@@ -70,7 +72,70 @@ def check_allreduce(comm, rank, world, dev):
             raise AssertionError(f"rank {rank}: fused sgd via {algo} diverged: {(p - ref_p).abs().max().item()}")
 
 
-def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overlap=True, algo="auto", graph=False):
+def check_fused_pack(comm, rank, world, dev):
+    """The pack prologue inside the allreduce kernel, on real peers: equal to dlb_pack + allreduce."""
+    from distributed_learning_b200.ops import fused as K
+
+    sizes = [1, 3, 7, 8, 64, 1000, 8191, 8192, 8193, 40003, 1 << 20]
+    variants = [("twoshot", 0), ("oneshot", 0)] + ([("nvls", 2), ("nvls", 4), ("nvls", 8)] if comm.has_multicast else [])
+    for flat_dtype, grad_dtype in ((torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16),
+                                   (torch.bfloat16, torch.float32)):
+        esize = 4 if flat_dtype == torch.float32 else 2
+        step = 16 // esize
+        offs, cur = [], 0
+        for n in sizes:
+            offs.append(cur)
+            cur = (cur + n + step - 1) // step * step
+        total = cur
+        g = torch.Generator(device=dev).manual_seed(4000 + rank)
+        grads = [torch.randn(n, device=dev, generator=g).to(grad_dtype) for n in sizes]
+        grads[3] = None
+        plan = K.PackPlan(sizes, offs, [grad_dtype] * len(sizes))
+        out_off = (total * esize + 4095) // 4096 * 4096
+        for algo, un in variants:
+            for nblocks in (4, 16):
+                # reference path: separate pack launch, then the allreduce
+                buf = comm.view(0, total, flat_dtype)
+                buf.fill_(float("nan"))
+                plan.pack(buf, grads, 1.0 / world)
+                comm.allreduce(0, total, flat_dtype, algo, scale=1.0, out_offset=out_off, nblocks=nblocks, unroll=un)
+                torch.cuda.synchronize()
+                want = (comm.view(out_off, total, flat_dtype) if algo == "oneshot" else buf).clone()
+                dist.barrier()
+                buf.fill_(float("nan"))
+                dist.barrier()
+                comm.allreduce(0, total, flat_dtype, algo, scale=1.0, out_offset=out_off, nblocks=nblocks, unroll=un,
+                               pack=plan.bind(grads), pack_scale=1.0 / world)
+                torch.cuda.synchronize()
+                got = comm.view(out_off, total, flat_dtype) if algo == "oneshot" else buf
+                if algo == "nvls":
+                    ok = torch.allclose(got.float(), want.float(), rtol=8e-3 if esize == 2 else 1e-5, atol=1e-5)
+                else:
+                    ok = torch.equal(got, want)
+                if not ok or bool(torch.isnan(got.float()).any()):
+                    raise AssertionError(f"rank {rank}: fused pack {algo}/u{un}/{nblocks} {flat_dtype}<-{grad_dtype} differs "
+                                         f"(max err {(got.float() - want.float()).abs().max().item()})")
+                dist.barrier()
+
+
+def check_broadcast(comm, rank, world, dev):
+    n = (3 << 20) + 16
+    buf = comm.view(0, n, torch.uint8)
+    for root in (0, world - 1):
+        g = torch.Generator(device=dev).manual_seed(70 + rank)
+        buf.copy_(torch.randint(0, 256, (n,), device=dev, generator=g, dtype=torch.uint8))
+        want = torch.randint(0, 256, (n,), device=dev, generator=torch.Generator(device=dev).manual_seed(70 + root),
+                             dtype=torch.uint8)
+        dist.barrier()
+        comm.broadcast(0, n, root=root)
+        torch.cuda.synchronize()
+        if not torch.equal(buf, want):
+            raise AssertionError(f"rank {rank}: broadcast from {root} differs")
+        dist.barrier()
+
+
+def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overlap=True, algo="auto", graph=False,
+                   fuse_pack=True):
     from distributed_learning_b200.models import CifarNet
     from distributed_learning_b200.parallel.graph_step import GraphedTrainStep
     from distributed_learning_b200.parallel.native import B200Dist
@@ -83,7 +148,7 @@ def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overl
         mdl.dropout1.p = 0.0
         mdl.dropout2.p = 0.0
     w = B200Dist(mine, None, 256 * 1024, dev, fused_sgd=fused, overlap=overlap, algo=algo, model_dtype=model_dtype,
-                 cuda_graph=graph)
+                 cuda_graph=graph, fuse_pack=fuse_pack)
     opt = w.make_optimizer(lr=0.01, momentum=0.5)
     ref_opt = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.5)
     g = torch.Generator(device=dev).manual_seed(500 + rank)
@@ -92,10 +157,9 @@ def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overl
     gstep = None
     for i, (x, y) in enumerate(batches):
         if graph:
-            if gstep is None:       # one eager warm-up step on batch 0, then capture; later batches are replays
+            if gstep is None:       # warm-up and capture leave no trace: every batch, the first included, is one replay
                 gstep = GraphedTrainStep(w, opt, x, y, warmup=1)
-            else:
-                gstep(x, y)
+            gstep(x, y)
         else:
             opt.zero_grad()
             F.nll_loss(w(x).float(), y).backward()
@@ -112,7 +176,7 @@ def check_training(rank, world, dev, comm, model_dtype="fp32", fused=True, overl
     for (n, p), q in zip(mine.named_parameters(), ref.parameters()):
         if not torch.allclose(p.float(), q, rtol=tol, atol=tol):
             raise AssertionError(f"rank {rank}: parameter {n} diverged ({(p.float() - q).abs().max().item()}) "
-                                 f"[{model_dtype} fused={fused} overlap={overlap} algo={algo} graph={graph}]")
+                                 f"[{model_dtype} fused={fused} overlap={overlap} algo={algo} graph={graph} fuse_pack={fuse_pack}]")
     # replicas bit-identical across ranks
     flat = torch.cat([p.detach().float().reshape(-1) for p in mine.parameters()])
     parts = [torch.empty_like(flat) for _ in range(world)]
@@ -182,13 +246,16 @@ def main():
         if rank == 0:
             print(f"arena mode {comm.mode}, multicast {comm.has_multicast} {comm.mc_note}")
         check_allreduce(comm, rank, world, dev)
+        check_fused_pack(comm, rank, world, dev)
+        check_broadcast(comm, rank, world, dev)
         comm.check()
         comm.close()
     os.environ.pop("DLB200_ARENA", None)
     if what in ("all", "train"):
         for kw in (dict(), dict(fused=False), dict(overlap=False), dict(algo="oneshot"), dict(algo="twoshot"),
                    dict(model_dtype="bf16"), dict(graph=True), dict(graph=True, algo="oneshot"),
-                   dict(graph=True, algo="twoshot", fused=False)):
+                   dict(graph=True, algo="twoshot", fused=False), dict(fuse_pack=False), dict(algo="nvls"),
+                   dict(model_dtype="bf16", algo="nvls", graph=True)):
             check_training(rank, world, dev, None, **kw)
     if what in ("all", "train", "reducer"):
         check_native_reducer(rank, world, dev)

@@ -128,3 +128,42 @@ def test_nvtx_ranges_do_not_disturb_a_step():
     t.end_step("x", {})
     assert float(loss) == float(loss) and t.rows()[0][1]["batch"] > 0
     w.cleanup()
+
+
+@pytest.mark.parametrize("algo", ["twoshot", "oneshot"])
+@pytest.mark.parametrize("dtype", ["fp32", "bf16"])
+@pytest.mark.parametrize("graph", [False, True])
+def test_whole_fused_gradient_path_on_one_gpu(algo, dtype, graph):
+    """comm_kernel_when_alone: the wrapper launches the fused kernel of the multi-GPU path (pack
+    prologue + barrier + reduce + SGD epilogue, one launch per bucket) with a world of one."""
+    from distributed_learning_b200.parallel.graph_step import GraphedTrainStep
+    from distributed_learning_b200.parallel.native import B200Dist
+
+    dev = torch.device("cuda:0")
+    torch.manual_seed(4)
+    ref = _TwoHeads().to(dev)
+    mine = copy.deepcopy(ref)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.5)
+    w = B200Dist(mine, None, 600, dev, algo=algo, model_dtype=dtype, comm_kernel_when_alone=True, cuda_graph=graph)
+    opt = w.make_optimizer(lr=0.1, momentum=0.5)
+    batches = [(torch.rand(8, 16, device=dev), torch.randint(4, (8,), device=dev)) for _ in range(4)]
+    step = None
+    for x, y in batches:
+        ropt.zero_grad()
+        F.nll_loss(ref(x), y).backward()
+        ropt.step()
+        if graph:
+            step = step or GraphedTrainStep(w, opt, x, y, warmup=2)
+            step(x, y)
+        else:
+            _native_step(w, opt, x, y)
+    torch.cuda.synchronize()
+    assert len(w.buckets) > 1
+    launches_per_step = w.kernel_launches / (len(batches) + (3 if graph else 0))
+    assert launches_per_step == len(w.buckets), "one kernel per bucket does pack, reduce and update"
+    tol = dict(rtol=1e-6, atol=1e-7) if dtype == "fp32" else dict(rtol=3e-2, atol=3e-3)
+    for (n, p), q in zip(ref.named_parameters(), mine.parameters()):
+        if not n.startswith("b."):
+            assert torch.allclose(p, q.float(), **tol), n
+    w.comm.check()
+    w.cleanup()
