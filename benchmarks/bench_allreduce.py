@@ -91,7 +91,7 @@ def main():
         print(f"arena {comm.mode}, multicast {comm.has_multicast} {comm.mc_note}", flush=True)
     blocks = [int(b) for b in args.blocks.split(",")]
     unrolls = [int(u) for u in args.unrolls.split(",")]
-    algos = ["oneshot", "twoshot"] + (["nvls"] if comm.has_multicast else [])
+    algos = ["oneshot", "twoshot", "twoshot_bulk"] + (["nvls"] if comm.has_multicast else [])
     if args.algos:
         algos = [a for a in args.algos.split(",") if a != "nvls" or comm.has_multicast]
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

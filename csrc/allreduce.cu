@@ -46,6 +46,7 @@
 
 #include <atomic>
 
+#include "bulk_copy.cuh"
 #include "sgd_math.cuh"
 #include "tensor_table.cuh"
 
@@ -281,6 +282,132 @@ __global__ void __launch_bounds__(512, 1) twoshot_pack_kernel(const __grid_const
                                                               const __grid_constant__ TensorTable tab) {
     __shared__ TableSmem ts;
     twoshot_body<T, NR, EMU, true>(a, &tab, &ts);
+}
+
+// ---- two-shot through the bulk-copy engine (cp.async.bulk, SASS UBLKCP) ------------------------------
+// Same algorithm, same column partition, same result as twoshot_body; what changes is who moves the
+// bytes.  One thread asks the copy engine for this CTA's tile of slice `rank` from every peer
+// (global -> shared, completion counted on an mbarrier, a three-stage ring keeps two tiles ahead in
+// flight), all threads sum the NR staged copies out of shared memory in rank order, and the reduced
+// tile leaves as NR bulk stores shared -> peer global.  The SM issues one instruction per peer per
+// 8 KB instead of one per 16 bytes, and no register holds data in flight.
+constexpr int kBulkArTileVec = 512;  // 16-byte vectors per tile = blockDim.x (one vector per thread)
+constexpr int kBulkArStages = 3;
+
+template <int R>
+struct BulkArSmem {
+    alignas(128) unsigned char in[kBulkArStages][R][kBulkArTileVec * 16];
+    alignas(128) unsigned char out[2][kBulkArTileVec * 16];
+    alignas(8) uint64_t full[kBulkArStages];
+};
+
+template <typename T, int NR, bool EMU, bool PACK>
+__device__ __forceinline__ void twoshot_bulk_body(const CommArgs& a, const TensorTable* tab, TableSmem* ts,
+                                                  BulkArSmem<Unroll<NR>::R>& sm) {
+    constexpr int N = VecOf<T>::N;
+    constexpr int R = Unroll<NR>::R;
+    const int nr = ranks_of<NR>(a);
+    const int rank = EMU ? (int)blockIdx.y : a.rank;
+    const int slot = EMU ? rank : 0;
+    uint32_t* state = a.state + (EMU ? rank * DLB_STATE_WORDS : 0);
+    uint32_t* err = state + DLB_MAX_BLOCKS;
+    uint32_t epoch = state[blockIdx.x];
+
+    trace_mark(a, slot, 0);
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kBulkArStages; ++i) mbar_init(&sm.full[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (PACK) {
+        table_stage(*ts, *tab, rank);
+        pack_columns<T, 1>(a, *ts, tab->ntensors, reinterpret_cast<char*>(a.buf[rank]), nr);
+    }
+    trace_mark(a, slot, 1);
+    block_barrier<NR>(a, rank, ++epoch, err);  // also makes the mbarrier initialisation visible to the CTA
+    trace_mark(a, slot, 2);
+
+    const int64_t slice = (a.nvec + nr - 1) / nr;
+    const int64_t begin = rank * slice, end = min(begin + slice, a.nvec);
+    const int64_t tile = blockDim.x;  // == kBulkArTileVec (checked by the host)
+    // this CTA's tiles of its slice: t0 = (blockIdx.x + i * gridDim.x) * tile, i = 0 .. mine-1
+    const int64_t have = end > begin ? end - begin : 0;
+    const int64_t ntiles = (have + tile - 1) / tile;
+    const int mine = (int64_t)blockIdx.x < ntiles ? (int)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+    auto tile_at = [&](int i, int64_t& j0, uint32_t& bytes) {
+        j0 = begin + ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * tile;
+        bytes = (uint32_t)(min(tile, end - j0) * 16);
+    };
+    auto issue_loads = [&](int i) {
+        int64_t j0;
+        uint32_t bytes;
+        tile_at(i, j0, bytes);
+        const int st = i % kBulkArStages;
+#pragma unroll
+        for (int p = 0; p < R; ++p)
+            if (p < nr) bulk_g2s(sm.in[st][p], reinterpret_cast<const char*>(a.buf[p]) + j0 * 16, bytes, &sm.full[st]);
+        mbar_arrive_expect_tx(&sm.full[st], bytes * nr);
+    };
+    if (threadIdx.x == 0) {
+        fence_proxy_async_all();  // the flags were acquired through the generic proxy; the engine reads after that
+        for (int i = 0; i < mine && i < kBulkArStages - 1; ++i) issue_loads(i);
+    }
+    for (int i = 0; i < mine; ++i) {
+        const int st = i % kBulkArStages;
+        if (threadIdx.x == 0) {
+            // stage (i-1) % S was read by every thread before the barrier that ended iteration i-1;
+            // out[i % 2] was last sent for tile i-2: at most the newest store group may still read
+            if (i + kBulkArStages - 1 < mine) issue_loads(i + kBulkArStages - 1);
+            bulk_wait_read<1>();
+        }
+        __syncthreads();
+        mbar_wait(&sm.full[st], (i / kBulkArStages) & 1);
+        int64_t j0;
+        uint32_t bytes;
+        tile_at(i, j0, bytes);
+        if (threadIdx.x * 16u < bytes) {
+            float acc[N];
+            VecOf<T>::to_float(reinterpret_cast<const vec16*>(sm.in[st][0])[threadIdx.x], acc);
+#pragma unroll
+            for (int p = 1; p < R; ++p)
+                if (p < nr) accumulate<T>(acc, reinterpret_cast<const vec16*>(sm.in[st][p])[threadIdx.x]);  // rank order
+#pragma unroll
+            for (int k = 0; k < N; ++k) acc[k] *= a.scale;
+            reinterpret_cast<vec16*>(sm.out[i & 1])[threadIdx.x] = VecOf<T>::from_float(acc);
+        }
+        fence_proxy_async_smem();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int p = 0; p < R; ++p)
+                if (p < nr) bulk_s2g(reinterpret_cast<char*>(a.buf[p]) + j0 * 16, sm.out[i & 1], bytes);
+            bulk_commit();
+        }
+    }
+    if (threadIdx.x == 0) {
+        bulk_wait_all<0>();       // every peer store of this CTA has been performed
+        fence_proxy_async_all();  // ... and is ordered before the generic-proxy release of the flags
+    }
+    trace_mark(a, slot, 3);
+
+    block_barrier<NR>(a, rank, ++epoch, err);  // all slices have landed in every buffer
+    trace_mark(a, slot, 4);
+
+    if (a.has_sgd) sgd_epilogue<T, 1>(a, a.sgd[slot], reinterpret_cast<const char*>(a.buf[rank]), nr);
+    if (threadIdx.x == 0) state[blockIdx.x] = epoch;
+    trace_mark(a, slot, 5);
+}
+
+template <typename T, int NR, bool EMU>
+__global__ void __launch_bounds__(512, 1) twoshot_bulk_kernel(const __grid_constant__ CommArgs a) {
+    extern __shared__ __align__(128) unsigned char bulk_ar_smem[];
+    twoshot_bulk_body<T, NR, EMU, false>(a, nullptr, nullptr, *reinterpret_cast<BulkArSmem<Unroll<NR>::R>*>(bulk_ar_smem));
+}
+template <typename T, int NR, bool EMU>
+__global__ void __launch_bounds__(512, 1) twoshot_bulk_pack_kernel(const __grid_constant__ CommArgs a,
+                                                                   const __grid_constant__ TensorTable tab) {
+    extern __shared__ __align__(128) unsigned char bulk_ar_smem[];
+    __shared__ TableSmem ts;
+    twoshot_bulk_body<T, NR, EMU, true>(a, &tab, &ts, *reinterpret_cast<BulkArSmem<Unroll<NR>::R>*>(bulk_ar_smem));
 }
 
 // ---- one-shot -------------------------------------------------------------------------------------
@@ -575,12 +702,13 @@ int fill_args(CommArgs& a, void* const* bufs, void* const* sigs, uint32_t* state
 }
 
 int launch(const void* k, dim3 grid, int threads, cudaStream_t stream, const CommArgs& a, const TensorTable* tab,
-           bool cooperative) {
+           bool cooperative, size_t smem = 0) {
     void* params[] = {const_cast<CommArgs*>(&a), const_cast<TensorTable*>(tab)};
+    if (smem > 48 * 1024) DLB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (cooperative)
-        DLB_CUDA(cudaLaunchCooperativeKernel(k, grid, dim3(threads), params, 0, stream));
+        DLB_CUDA(cudaLaunchCooperativeKernel(k, grid, dim3(threads), params, smem, stream));
     else
-        DLB_CUDA(cudaLaunchKernel(k, grid, dim3(threads), params, 0, stream));
+        DLB_CUDA(cudaLaunchKernel(k, grid, dim3(threads), params, smem, stream));
     return 0;
 }
 
@@ -599,6 +727,14 @@ template <bool EMU>
 const void* pick_oneshot(int dtype, int nranks, bool pack) {
     if (dtype == DLB_F32) return pack ? PICK_NR(oneshot_pack_kernel, float, EMU, nranks) : PICK_NR(oneshot_kernel, float, EMU, nranks);
     return pack ? PICK_NR(oneshot_pack_kernel, __nv_bfloat16, EMU, nranks) : PICK_NR(oneshot_kernel, __nv_bfloat16, EMU, nranks);
+}
+
+template <bool EMU>
+const void* pick_twoshot_bulk(int dtype, int nranks, bool pack, size_t* smem) {
+    *smem = nranks == 2 ? sizeof(BulkArSmem<2>) : nranks == 4 ? sizeof(BulkArSmem<4>) : sizeof(BulkArSmem<DLB_MAX_RANKS>);
+    if (dtype == DLB_F32)
+        return pack ? PICK_NR(twoshot_bulk_pack_kernel, float, EMU, nranks) : PICK_NR(twoshot_bulk_kernel, float, EMU, nranks);
+    return pack ? PICK_NR(twoshot_bulk_pack_kernel, __nv_bfloat16, EMU, nranks) : PICK_NR(twoshot_bulk_kernel, __nv_bfloat16, EMU, nranks);
 }
 
 #define PICK_UT(KERNEL, T, ut) ((ut) == 2 ? (const void*)KERNEL<T, 2> : (ut) == 4 ? (const void*)KERNEL<T, 4> : (const void*)KERNEL<T, 8>)
@@ -650,9 +786,9 @@ extern "C" int dlb_comm_check(uint32_t* state, void* stream) {
 // ---- the general entry point ----------------------------------------------------------------------------
 extern "C" int dlb_allreduce(const dlb_allreduce_desc_t* d, void* stream) {
     DLB_REQUIRE(d != nullptr, DLB_E_ARG, "dlb_allreduce: null descriptor");
-    const char* who = d->algo == DLB_ALGO_TWOSHOT ? "dlb_allreduce(twoshot)" : d->algo == DLB_ALGO_ONESHOT ? "dlb_allreduce(oneshot)" : "dlb_allreduce(nvls)";
-    DLB_REQUIRE(d->algo == DLB_ALGO_TWOSHOT || d->algo == DLB_ALGO_ONESHOT || d->algo == DLB_ALGO_NVLS, DLB_E_ARG,
-                "dlb_allreduce: unknown algo %d", d->algo);
+    const char* who = d->algo == DLB_ALGO_TWOSHOT ? "dlb_allreduce(twoshot)" : d->algo == DLB_ALGO_ONESHOT ? "dlb_allreduce(oneshot)"
+                      : d->algo == DLB_ALGO_NVLS  ? "dlb_allreduce(nvls)" : "dlb_allreduce(twoshot_bulk)";
+    DLB_REQUIRE(d->algo >= DLB_ALGO_TWOSHOT && d->algo <= DLB_ALGO_TWOSHOT_BULK, DLB_E_ARG, "dlb_allreduce: unknown algo %d", d->algo);
     DLB_REQUIRE(d->bufs != nullptr, DLB_E_ARG, "%s: null bufs", who);
     CommArgs a;
     int rc = fill_args(a, d->bufs, d->sigs, d->state, d->rank, d->nranks, d->numel, d->dtype, d->scale, d->nblocks, d->nthreads, d->sgd, who);
@@ -666,8 +802,12 @@ extern "C" int dlb_allreduce(const dlb_allreduce_desc_t* d, void* stream) {
     a.pack_scale = d->pack_scale == 0.f ? 1.f : d->pack_scale;
     a.trace = d->trace;
     const void* k = nullptr;
+    size_t smem = 0;
     if (d->algo == DLB_ALGO_TWOSHOT) {
         k = pick_twoshot<false>(d->dtype, d->nranks, pack);
+    } else if (d->algo == DLB_ALGO_TWOSHOT_BULK) {
+        DLB_REQUIRE(d->nthreads == kBulkArTileVec, DLB_E_ARG, "%s: needs %d threads per CTA (one 16-byte vector of the tile each)", who, kBulkArTileVec);
+        k = pick_twoshot_bulk<false>(d->dtype, d->nranks, pack, &smem);
     } else if (d->algo == DLB_ALGO_ONESHOT) {
         DLB_REQUIRE(d->out != nullptr || d->sgd != nullptr, DLB_E_ARG, "%s: neither an output buffer nor a fused update", who);
         DLB_REQUIRE(d->out != d->bufs[d->rank], DLB_E_ARG, "%s: out may not alias the input buffer (peers are reading it)", who);
@@ -681,7 +821,7 @@ extern "C" int dlb_allreduce(const dlb_allreduce_desc_t* d, void* stream) {
         a.mc = d->mc_buf;
         k = pick_nvls(d->dtype, unroll, pack);
     }
-    return launch(k, dim3(d->nblocks), d->nthreads, (cudaStream_t)stream, a, pack ? &tab : nullptr, false);
+    return launch(k, dim3(d->nblocks), d->nthreads, (cudaStream_t)stream, a, pack ? &tab : nullptr, false, smem);
 }
 
 // ---- the original entry points: thin wrappers ------------------------------------------------------------
@@ -789,8 +929,10 @@ extern "C" size_t dlb_emulated_flags_bytes(int nranks) {
 extern "C" int dlb_allreduce_emulated_ex(const dlb_emulated_desc_t* d, void* stream) {
     DLB_REQUIRE(d != nullptr, DLB_E_ARG, "dlb_allreduce_emulated: null descriptor");
     DLB_REQUIRE(d->flags != nullptr && d->bufs != nullptr, DLB_E_ARG, "dlb_allreduce_emulated: null argument");
-    DLB_REQUIRE(d->algo == DLB_ALGO_TWOSHOT || d->algo == DLB_ALGO_ONESHOT, DLB_E_ARG,
-                "dlb_allreduce_emulated: algo must be 0 (two-shot) or 1 (one-shot)");
+    DLB_REQUIRE(d->algo == DLB_ALGO_TWOSHOT || d->algo == DLB_ALGO_ONESHOT || d->algo == DLB_ALGO_TWOSHOT_BULK, DLB_E_ARG,
+                "dlb_allreduce_emulated: algo must be 0 (two-shot), 1 (one-shot) or 3 (two-shot through the bulk-copy engine)");
+    DLB_REQUIRE(d->algo != DLB_ALGO_TWOSHOT_BULK || d->nthreads == kBulkArTileVec, DLB_E_ARG,
+                "dlb_allreduce_emulated: the bulk-copy variant needs %d threads per CTA", kBulkArTileVec);
     const int nranks = d->nranks;
     DLB_REQUIRE(nranks >= 1 && nranks <= DLB_MAX_RANKS, DLB_E_LIMIT, "dlb_allreduce_emulated: nranks %d outside 1..%d", nranks, DLB_MAX_RANKS);
     void* sigs[DLB_MAX_RANKS];
@@ -818,8 +960,11 @@ extern "C" int dlb_allreduce_emulated_ex(const dlb_emulated_desc_t* d, void* str
     a.pack_scale = d->pack_scale == 0.f ? 1.f : d->pack_scale;
     a.trace = d->trace;
     // all nranks * nblocks CTAs must be co-resident: that is what the cooperative launch checks
-    const void* k = d->algo == DLB_ALGO_TWOSHOT ? pick_twoshot<true>(d->dtype, nranks, pack) : pick_oneshot<true>(d->dtype, nranks, pack);
-    return launch(k, dim3(d->nblocks, nranks), d->nthreads, (cudaStream_t)stream, a, pack ? &tab : nullptr, true);
+    size_t smem = 0;
+    const void* k = d->algo == DLB_ALGO_TWOSHOT        ? pick_twoshot<true>(d->dtype, nranks, pack)
+                    : d->algo == DLB_ALGO_TWOSHOT_BULK ? pick_twoshot_bulk<true>(d->dtype, nranks, pack, &smem)
+                                                       : pick_oneshot<true>(d->dtype, nranks, pack);
+    return launch(k, dim3(d->nblocks, nranks), d->nthreads, (cudaStream_t)stream, a, pack ? &tab : nullptr, true, smem);
 }
 
 extern "C" int dlb_allreduce_emulated(int algo, void* const* bufs, void* const* outs, const dlb_fused_sgd_t* sgds,

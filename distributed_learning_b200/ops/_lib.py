@@ -57,7 +57,7 @@ class EmulatedDesc(ctypes.Structure):
                 ("numels", POINTER(c_int64)), ("ntensors", c_int), ("pack_scale", c_float), ("trace", c_void_p)]
 
 
-ALGO_CODE = {"twoshot": 0, "oneshot": 1, "nvls": 2}
+ALGO_CODE = {"twoshot": 0, "oneshot": 1, "nvls": 2, "twoshot_bulk": 3}
 
 
 class DlbError(RuntimeError):

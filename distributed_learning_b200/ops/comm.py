@@ -27,7 +27,7 @@ import torch
 from ._lib import (ALGO_CODE, DLB_MAX_BLOCKS, DLB_MAX_RANKS, DLB_SIGNAL_BYTES, DLB_STATE_WORDS, AllreduceDesc, DlbError,
                    EmulatedDesc, FusedSgd, check, dtype_code, lib, ptr_array, stream_handle)
 
-ALGOS = ("oneshot", "twoshot", "nvls")
+ALGOS = ("oneshot", "twoshot", "nvls")         # what `tune` tries; "twoshot_bulk" is opt-in (--algo)
 _ALIGN = 4096
 
 

@@ -63,7 +63,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--checkpoint", type=str, default=None, help="checkpoint file (torch state_dict format)")
     p.add_argument("--checkpoint_every", type=int, default=0, help="save every N batches (0: only at the end)")
     p.add_argument("--resume", type=int, default=0, help="resume from --checkpoint if it exists")
-    p.add_argument("--algo", type=str, default="auto", choices=("auto", "oneshot", "twoshot", "nvls", "nvls_deep"),
+    p.add_argument("--algo", type=str, default="auto", choices=("auto", "oneshot", "twoshot", "twoshot_bulk", "nvls", "nvls_deep"),
                    help="native allreduce variant (auto: chosen per message size from measured bus bandwidth)")
     p.add_argument("--fused_sgd", type=int, default=1, help="b200 backend: apply SGD inside/after the allreduce kernel on the flat buffers")
     p.add_argument("--fuse_pack", type=int, default=1, help="b200 backend: gather the gradients inside the allreduce kernel (one launch per bucket) instead of a separate pack launch")

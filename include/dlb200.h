@@ -193,7 +193,13 @@ int dlb_allreduce_nvls_deep(void* mc_buf, void* const* bufs, void* const* sigs, 
  *           pass the same value (it sets the tile that CTAs own).
  *   trace   optional device pointer to 8 uint64: %globaltimer (ns) of CTA 0 at start, packed, entry
  *           barrier passed, data phase done, exit barrier passed, epilogue done. */
-enum { DLB_ALGO_TWOSHOT = 0, DLB_ALGO_ONESHOT = 1, DLB_ALGO_NVLS = 2 };
+enum {
+    DLB_ALGO_TWOSHOT = 0,
+    DLB_ALGO_ONESHOT = 1,
+    DLB_ALGO_NVLS = 2,
+    DLB_ALGO_TWOSHOT_BULK = 3 /* two-shot with the bytes moved by the bulk-copy engine (cp.async.bulk + mbarrier through a
+                                 shared-memory ring; 512 threads per CTA); same result as DLB_ALGO_TWOSHOT */
+};
 
 typedef struct {
     int algo, rank, nranks;

@@ -22,7 +22,7 @@ def gathered_sum(x, world, scale, dtype):
 def check_allreduce(comm, rank, world, dev):
     from distributed_learning_b200.ops import fused as K
 
-    algos = ["twoshot", "oneshot"] + (["nvls", "nvls_u2", "nvls_u8"] if comm.has_multicast else [])
+    algos = ["twoshot", "oneshot", "twoshot_bulk"] + (["nvls", "nvls_u2", "nvls_u8"] if comm.has_multicast else [])
     for dtype in (torch.float32, torch.bfloat16):
         esize = 4 if dtype == torch.float32 else 2
         for numel in (16, 4096, 100000 // 8 * 8, 1 << 22):
@@ -77,7 +77,7 @@ def check_fused_pack(comm, rank, world, dev):
     from distributed_learning_b200.ops import fused as K
 
     sizes = [1, 3, 7, 8, 64, 1000, 8191, 8192, 8193, 40003, 1 << 20]
-    variants = [("twoshot", 0), ("oneshot", 0)] + ([("nvls", 2), ("nvls", 4), ("nvls", 8)] if comm.has_multicast else [])
+    variants = [("twoshot", 0), ("oneshot", 0), ("twoshot_bulk", 0)] + ([("nvls", 2), ("nvls", 4), ("nvls", 8)] if comm.has_multicast else [])
     for flat_dtype, grad_dtype in ((torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16),
                                    (torch.bfloat16, torch.float32)):
         esize = 4 if flat_dtype == torch.float32 else 2

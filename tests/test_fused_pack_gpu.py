@@ -36,7 +36,7 @@ def _reference(stacked, offs, total, nranks, flat_dtype, pack_scale, scale):
     return (acc * scale).to(flat_dtype), bufs
 
 
-@pytest.mark.parametrize("algo", ["twoshot", "oneshot"])
+@pytest.mark.parametrize("algo", ["twoshot", "oneshot", "twoshot_bulk"])
 @pytest.mark.parametrize("nranks", [2, 3, 4, 8])
 @pytest.mark.parametrize("flat_dtype,grad_dtype", [(torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16),
                                                    (torch.bfloat16, torch.float32), (torch.float32, torch.bfloat16)])
@@ -57,6 +57,8 @@ def test_fused_pack_equals_pack_then_allreduce(algo, nranks, flat_dtype, grad_dt
     plan = K.PackPlan(sizes, offs, [grad_dtype] * len(sizes)).bind(stacked)
     nan = float("nan")
     for nblocks, nthreads in ((3, 128), (8, 512)):
+        if algo == "twoshot_bulk" and nthreads != 512:
+            continue                       # one 16-byte vector of the 8 KB tile per thread
         bufs = [torch.full((total,), nan, device=dev, dtype=flat_dtype) for _ in range(nranks)]
         outs = [torch.full((total,), nan, device=dev, dtype=flat_dtype) for _ in range(nranks)] if algo == "oneshot" else None
         C.emulated_allreduce(bufs, algo, scale=scale, outs=outs, nblocks=nblocks, nthreads=nthreads, pack=plan,
@@ -64,7 +66,9 @@ def test_fused_pack_equals_pack_then_allreduce(algo, nranks, flat_dtype, grad_dt
         # the two launches it replaces
         bufs2 = [p.clone() for p in packed]
         outs2 = [torch.empty_like(b) for b in bufs2] if algo == "oneshot" else None
-        C.emulated_allreduce(bufs2, algo, scale=scale, outs=outs2, nblocks=nblocks, nthreads=nthreads)
+        # (for the bulk-copy variant the reference is the plain two-shot kernel: same sums, other engine)
+        C.emulated_allreduce(bufs2, "twoshot" if algo == "twoshot_bulk" else algo, scale=scale, outs=outs2, nblocks=nblocks,
+                             nthreads=nthreads)
         torch.cuda.synchronize()
         got, got2 = (outs, outs2) if algo == "oneshot" else (bufs, bufs2)
         for r in range(nranks):
@@ -91,12 +95,12 @@ def test_fused_pack_with_fused_sgd_is_one_launch_for_the_whole_gradient_path():
     ref_p.grad = want.clone()
     opt.step()
     hyper = K.make_hyper(0.01, 0.5)
-    for algo in ("twoshot", "oneshot"):
+    for algo in ("twoshot", "oneshot", "twoshot_bulk"):
         params = [p0.clone() for _ in range(nranks)]
         moms = [torch.zeros(total, device=dev) for _ in range(nranks)]
         bufs = [torch.zeros(total, device=dev) for _ in range(nranks)]
         plan = K.PackPlan(sizes, offs, [torch.float32] * 3).bind(stacked)
-        C.emulated_allreduce(bufs, algo, scale=1.0, nblocks=4, nthreads=256, pack=plan, pack_scale=0.25,
+        C.emulated_allreduce(bufs, algo, scale=1.0, nblocks=4, nthreads=512 if algo == "twoshot_bulk" else 256, pack=plan, pack_scale=0.25,
                              sgds=[K.fused_sgd_args(p, m, hyper) for p, m in zip(params, moms)])
         torch.cuda.synchronize()
         for r in range(nranks):
@@ -126,3 +130,26 @@ def test_phase_trace_is_monotonic():
     torch.cuda.synchronize()
     t = trace.view(4, 8)[:, :6].cpu()
     assert bool((t[:, 1:] >= t[:, :-1]).all()) and bool((t[:, 5] > t[:, 0]).all())
+
+
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_bulk_copy_twoshot_equals_twoshot_over_many_tiles(nranks, dtype):
+    """Sizes that give a CTA zero, one and many tiles, a short last tile, and repeated launches on one
+    flag buffer (mbarrier phases and epochs carry over nothing between launches)."""
+    from distributed_learning_b200.ops import comm as C
+
+    dev = torch.device("cuda:0")
+    per = 4 if dtype == torch.float32 else 8
+    flags = C.emulated_flags(nranks, dev)
+    for numel in (per, 512 * per, 5000 * per, (1 << 20) + 24 * per):
+        for nblocks in (1, 5):
+            g = torch.Generator(device=dev).manual_seed(numel + nblocks)
+            src = [torch.randn(numel, device=dev, generator=g).to(dtype) for _ in range(nranks)]
+            a = [x.clone() for x in src]
+            b = [x.clone() for x in src]
+            C.emulated_allreduce(a, "twoshot_bulk", scale=1.0 / nranks, flags=flags, nblocks=nblocks, nthreads=512)
+            C.emulated_allreduce(b, "twoshot", scale=1.0 / nranks, nblocks=nblocks, nthreads=512)
+            torch.cuda.synchronize()
+            for r in range(nranks):
+                assert torch.equal(a[r], b[r]), (numel, nblocks, r)
