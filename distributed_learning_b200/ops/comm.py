@@ -47,25 +47,39 @@ def tensor_from_ptr(ptr: int, nbytes: int, device) -> torch.Tensor:
     return torch.as_tensor(_RawCudaMemory(ptr, nbytes), device=device)
 
 
-def default_nblocks(nbytes: int, algo: str) -> int:
+# HBM bytes per second that ONE CTA (512 threads) of a communication kernel sustains in its pack
+# prologue and SGD epilogue: ncu of the fused kernels on real peers, 16 MiB with 32 CTAs, shows
+# 117 MB of pack + update traffic in ~69 us on top of the bare allreduce at 2 and at 8 GPUs
+# (profiles/ncu/r2_nvlink_n{2,8}_durations.csv).
+FUSED_HBM_BYTES_PER_S_PER_CTA = 53e9
+
+
+def default_nblocks(nbytes: int, algo: str, hbm_bytes: int = 0) -> int:
+    """CTAs when nothing was measured.  From the 2/4/8-GPU sweeps (profiles/results/r2_suite_n*): the
+    switch-reduced variant is fastest with few CTAs (16) at every size, the peer-to-peer variants
+    want more as the message grows; a kernel that also packs and updates (``hbm_bytes`` > 0) is bound
+    by how many SMs stream its HBM traffic and takes the full grid from 1 MiB up."""
     env = os.environ.get("DLB200_NBLOCKS")
     if env:
         return max(1, min(DLB_MAX_BLOCKS, int(env)))
-    if nbytes <= 256 << 10:
-        return 8
-    if nbytes <= 4 << 20:
+    if hbm_bytes > 0 and nbytes >= 1 << 20:
+        return DLB_MAX_BLOCKS
+    if algo == "nvls":
         return 16
-    if nbytes <= 32 << 20:
+    if nbytes <= 256 << 10:
+        return 16
+    if nbytes <= 4 << 20:
         return 32
-    return 48
+    return 64
 
 
 def default_unroll(nbytes: int) -> int:
-    """nvls pipeline depth when nothing was measured: deeper for larger messages."""
+    """nvls pipeline depth when nothing was measured: 4 reductions in flight per thread won or tied
+    at every size of the 4- and 8-GPU sweeps (8 is 2-30 % slower from 16 MiB up)."""
     env = os.environ.get("DLB200_UNROLL")
     if env:
         return int(env)
-    return 4 if nbytes <= 2 << 20 else 8
+    return 4
 
 
 class _ModeFailed(RuntimeError):
@@ -97,6 +111,7 @@ class NativeComm:
         self._buf_arrays: Dict[int, "ctypes.Array"] = {}
         self._handles: dict = {}
         self.tuned: Dict[Tuple[int, int], Tuple[str, int, int]] = {}     # (dtype code, pow2 bytes) -> (algo, nblocks, unroll)
+        self.tuned_ms: Dict[Tuple[int, int], Dict[Tuple[str, int, int], float]] = {}   # ... -> every candidate's time
         self.launches = 0
         self.topology: Optional[dict] = None
 
@@ -360,22 +375,39 @@ class NativeComm:
     # ---------------------------------------------------------------------------------------
     # collectives
     # ---------------------------------------------------------------------------------------
-    def choose(self, nbytes: int, dtype: torch.dtype, algo: str = "auto") -> Tuple[str, int, int]:
-        """``(variant, CTAs, unroll)`` for a message: the measured table if ``tune`` filled it, else a
-        size heuristic (one-shot while latency dominates, NVLS when the switch can reduce)."""
+    def choose(self, nbytes: int, dtype: torch.dtype, algo: str = "auto", hbm_bytes: int = 0) -> Tuple[str, int, int]:
+        """``(variant, CTAs, unroll)`` for a message: from the measured table if ``tune`` filled it, else
+        a size heuristic (one-shot while latency dominates, NVLS when the switch can reduce).
+
+        ``hbm_bytes``: local HBM traffic of the prologue and epilogue fused into the kernel (pack:
+        2 bytes moved per buffer byte; fp32 SGD: 5).  ``tune`` times the bare allreduce, where the
+        switch-reduced variant is fastest on 8-16 CTAs; a kernel that also streams several times the
+        buffer through HBM on those few SMs would be far slower than the allreduce it saves, so the
+        fused choice minimises  measured allreduce time + hbm_bytes / (CTAs x per-CTA bandwidth)."""
         if algo != "auto":
             unroll = 8 if algo == "nvls_deep" else default_unroll(nbytes)
             if algo in ("nvls", "nvls_deep"):
                 algo = "nvls" if self.has_multicast else "twoshot"
-            return algo, default_nblocks(nbytes, algo), unroll
+            return algo, default_nblocks(nbytes, algo, hbm_bytes), unroll
         key = (dtype_code(dtype), max(nbytes, 1).bit_length())
+        table = self.tuned_ms.get(key)
+        if table and hbm_bytes > 0:
+            def cost(item):
+                (_, nb, _), ms = item
+                return ms + hbm_bytes / (nb * FUSED_HBM_BYTES_PER_S_PER_CTA) * 1e3
+            return min(table.items(), key=cost)[0]
         if key in self.tuned:
-            return self.tuned[key]
-        if nbytes <= (256 << 10) * 8 // max(self.world, 2):
-            return "oneshot", default_nblocks(nbytes, "oneshot"), 0
-        if self.has_multicast:
-            return "nvls", default_nblocks(nbytes, "nvls"), default_unroll(nbytes)
-        return "twoshot", default_nblocks(nbytes, "twoshot"), 0
+            best = self.tuned[key]
+            if hbm_bytes > 0:                    # only the winner is known (cached table): keep its variant
+                return best[0], max(best[1], default_nblocks(nbytes, best[0], hbm_bytes)), best[2]
+            return best
+        if self.has_multicast and self.world >= 4:
+            if nbytes <= 512 << 10:
+                return "oneshot", default_nblocks(nbytes, "oneshot", hbm_bytes), 0
+            return "nvls", default_nblocks(nbytes, "nvls", hbm_bytes), default_unroll(nbytes)
+        if nbytes * (self.world - 1) <= 16 << 20:
+            return "oneshot", default_nblocks(nbytes, "oneshot", hbm_bytes), 0
+        return "twoshot", default_nblocks(nbytes, "twoshot", hbm_bytes), 0
 
     def allreduce(self, offset: int, numel: int, dtype: torch.dtype, algo: str = "twoshot", scale: float = 1.0,
                   out_offset: Optional[int] = None, sgd: Optional[FusedSgd] = None, nblocks: Optional[int] = None,
@@ -532,12 +564,13 @@ class NativeComm:
                 t = t.cpu()
             best = int(torch.argmin(t))
             self.tuned[(dtype_code(dtype), max(nbytes, 1).bit_length())] = keys[best]
+            self.tuned_ms[(dtype_code(dtype), max(nbytes, 1).bit_length())] = dict(zip(keys, t.tolist()))
             report[nbytes] = {"best": keys[best], "ms": {f"{a}/{b}/u{u}": float(v) for (a, b, u), v in zip(keys, t.tolist())}}
         if cache:
             self._save_tuned()
         return report
 
-    # the measured table on disk: {"<dtype code>:<size class>": [algo, nblocks, unroll]}
+    # the measured table on disk: {"<dtype code>:<size class>": {"best": [algo, nblocks, unroll], "ms": {"algo/nblocks/unroll": ms}}}
     def _tune_cache_path(self) -> str:
         import re
         import tempfile
@@ -561,13 +594,23 @@ class NativeComm:
             except (OSError, ValueError):
                 table = None
         table = self._gather(table)[0] if self.world > 1 else table
-        if not table:
+        if not isinstance(table, dict) or not table:
             return False
-        for k, v in table.items():
-            code, cls = k.split(":")
-            if v[0] == "nvls" and not self.has_multicast:
-                continue
-            self.tuned.setdefault((int(code), int(cls)), (v[0], int(v[1]), int(v[2])))
+        try:
+            for k, v in table.items():
+                code, cls = (int(x) for x in k.split(":"))
+                best = v["best"]
+                if best[0] == "nvls" and not self.has_multicast:
+                    continue
+                self.tuned.setdefault((code, cls), (best[0], int(best[1]), int(best[2])))
+                ms = {}
+                for name, t in v.get("ms", {}).items():
+                    a, nb, un = name.split("/")
+                    ms[(a, int(nb), int(un))] = float(t)
+                if ms:
+                    self.tuned_ms.setdefault((code, cls), ms)
+        except (KeyError, ValueError, TypeError, IndexError):
+            return False                          # a file of another version: measure again
         return True
 
     def _save_tuned(self) -> None:
@@ -580,9 +623,13 @@ class NativeComm:
             try:
                 with open(path) as f:
                     table = json.load(f)
+                if not isinstance(table, dict):
+                    table = {}
             except (OSError, ValueError):
                 table = {}
-            table.update({f"{c}:{cls}": list(v) for (c, cls), v in self.tuned.items()})
+            for (c, cls), best in self.tuned.items():
+                ms = self.tuned_ms.get((c, cls), {})
+                table[f"{c}:{cls}"] = {"best": list(best), "ms": {f"{a}/{nb}/{un}": t for (a, nb, un), t in ms.items()}}
             with open(path + f".{os.getpid()}", "w") as f:
                 json.dump(table, f)
             os.replace(path + f".{os.getpid()}", path)

@@ -255,7 +255,8 @@ class B200Dist(_Wrapper):
             nb.regions = [self.comm.view(o, nb.numel, self.comm_dtype) for o in nb.region_offsets]
             nb.b.grad_buffer = nb.regions[0]
             if world > 1 or self.comm_kernel_when_alone:
-                nb.algo, nb.nblocks, nb.unroll = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
+                nb.algo, nb.nblocks, nb.unroll = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo,
+                                                                  hbm_bytes=self._fused_hbm_bytes(nb.numel, esize))
             self._flatten_parameters(nb)
         d["buckets"] = buckets
         if world > 1 and self.sync_initial_state:
@@ -278,11 +279,23 @@ class B200Dist(_Wrapper):
             sizes = sorted({nb.numel * esize for nb in buckets})
             self.comm.tune(sizes, self.comm_dtype)
             for nb in buckets:
-                nb.algo, nb.nblocks, nb.unroll = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo)
+                nb.algo, nb.nblocks, nb.unroll = self.comm.choose(nb.numel * esize, self.comm_dtype, self.algo,
+                                                                  hbm_bytes=self._fused_hbm_bytes(nb.numel, esize))
         print_d("B200Dist: " + ", ".join(f"bucket{nb.id}: {len(nb.tensors)} tensors {nb.numel * esize / 2**20:.2f} MiB "
                                          f"{nb.algo}/{nb.nblocks}" + (f"/u{nb.unroll}" if nb.algo == "nvls" else "") for nb in buckets)
                 + f" (arena {self.comm.mode}, multicast {'yes' if self.comm.has_multicast else 'no'}"
                 + (f": {self.comm.mc_note}" if self.comm.mc_note else "") + ")", Level.INFO)
+
+    def _fused_hbm_bytes(self, numel: int, esize: int) -> int:
+        """Local HBM traffic that rides in a bucket's kernel besides the allreduce: the pack prologue
+        reads the gradients and writes the buffer; the SGD epilogue reads the reduced gradient, the
+        fp32 parameter and momentum and writes both back (plus the bf16 copy for bf16 models)."""
+        total = 0
+        if self.fuse_pack:
+            total += 2 * numel * esize
+        if self.fused_sgd:
+            total += numel * (esize + 16 + (2 if self.model_dtype == torch.bfloat16 else 0))
+        return total
 
     def _flatten_parameters(self, nb: _NativeBucket) -> None:
         """Re-home the bucket's parameters in one flat fp32 buffer (and a bf16 copy for bf16

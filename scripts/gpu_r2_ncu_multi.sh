@@ -15,19 +15,20 @@ plain() {   # the whole job without a profiler
 attempt() {  # $1 = name, $2 = port base, rest = ncu arguments
   local name=$1 port=$2; shift 2
   rm -f /tmp/nvl_run_*; export NVL_PORT=$port
-  # peers may be started several times: ncu may run rank 0's command more than once
-  for r in $(seq 1 $((N-1))); do
-    ( for i in 1 2 3; do NVL_RANK=$r timeout 150 python profiles/nvlink_worker.py > $out/${name}_peer_${r}_$i.log 2>&1 || break; done ) &
-  done
   NVL_RANK=0 timeout 400 ncu "$@" --clock-control none --cache-control none -k regex:'twoshot|oneshot|nvls' -c 8 \
-     --csv --log-file $out/${name}_rank0.csv python profiles/nvlink_worker.py > $out/${name}_rank0.log 2>&1
-  echo "$name: ncu exit $?"
+     --csv --log-file $out/${name}_rank0.csv python profiles/nvlink_worker.py > $out/${name}_rank0.log 2>&1 &
+  local ncu_pid=$!
+  # peers: ncu may run rank 0's command more than once, so a peer starts again for as long as ncu is alive
+  for r in $(seq 1 $((N-1))); do
+    ( i=0; while kill -0 $ncu_pid 2>/dev/null && [ $i -lt 3 ]; do i=$((i+1))
+        NVL_RANK=$r timeout 150 python profiles/nvlink_worker.py > $out/${name}_peer_${r}_$i.log 2>&1 || break; done ) &
+  done
+  wait $ncu_pid; echo "$name: ncu exit $?"
   wait
-  tail -4 $out/${name}_rank0.log
-  head -c 2500 $out/${name}_rank0.csv; echo
+  tail -3 $out/${name}_rank0.log
+  head -c 1500 $out/${name}_rank0.csv; echo
 }
 
 plain 29700
-attempt app 29720 --replay-mode application --metrics $M_NVL
 attempt kern_time 29740 --metrics gpu__time_duration.sum
 attempt kern_nvl 29760 --metrics nvlrx__bytes.sum,nvltx__bytes.sum

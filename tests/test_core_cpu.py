@@ -261,3 +261,44 @@ def test_launcher_port_and_backend_selection(monkeypatch):
     n = parse_args(["1", "0", "1", "1", "a", "i", "mnist", "/r", "1", "--backend", "nccl"])
     assert launcher._group_backend(n, one_process_per_gpu=True) == "cpu:gloo,cuda:nccl"
     assert launcher._group_backend(parse_args(ARGV), True) == "gloo"
+
+
+# ---- variant / grid selection of the native communicator (pure host logic) -------------------------
+def _fake_comm(world, multicast):
+    from distributed_learning_b200.ops.comm import NativeComm
+
+    c = object.__new__(NativeComm)
+    c.world, c.rank, c.mc_ptr = world, 0, (1 if multicast else None)
+    c.tuned, c.tuned_ms = {}, {}
+    c._gather = lambda obj: [obj] * world          # stands in for the collective: every rank sees rank 0's object
+    return c
+
+
+def test_choose_heuristics_and_fused_cost_model(tmp_path, monkeypatch):
+    from distributed_learning_b200.ops._lib import dtype_code
+
+    c8 = _fake_comm(8, True)
+    assert c8.choose(64 << 10, torch.float32)[0] == "oneshot"
+    assert c8.choose(16 << 20, torch.float32) == ("nvls", 16, 4)
+    assert c8.choose(16 << 20, torch.float32, hbm_bytes=7 * (16 << 20)) == ("nvls", 64, 4), "a fused kernel takes the full grid"
+    c2 = _fake_comm(2, True)
+    assert c2.choose(4 << 20, torch.float32)[0] == "oneshot" and c2.choose(64 << 20, torch.float32)[0] == "twoshot"
+    assert _fake_comm(8, False).choose(16 << 20, torch.float32)[0] == "twoshot"
+    assert c8.choose(16 << 20, torch.float32, algo="nvls_deep") == ("nvls", 16, 8)
+    assert _fake_comm(8, False).choose(16 << 20, torch.float32, algo="nvls")[0] == "twoshot"
+
+    # measured table: the bare allreduce is fastest on 8 CTAs, the fused kernel is not
+    key = (dtype_code(torch.float32), (24 << 20).bit_length())
+    c8.tuned[key] = ("nvls", 8, 4)
+    c8.tuned_ms[key] = {("nvls", 8, 4): 0.060, ("nvls", 16, 4): 0.062, ("nvls", 64, 4): 0.075, ("twoshot", 64, 0): 0.080}
+    assert c8.choose(24 << 20, torch.float32) == ("nvls", 8, 4)
+    assert c8.choose(24 << 20, torch.float32, hbm_bytes=7 * (24 << 20)) == ("nvls", 64, 4)
+    assert c8.choose(24 << 20, torch.float32, hbm_bytes=1 << 10) == ("nvls", 8, 4), "negligible extra traffic changes nothing"
+
+    # the table survives a round trip through the cache file
+    monkeypatch.setenv("DLB200_TUNE_CACHE", str(tmp_path / "tune.json"))
+    c8._save_tuned()
+    fresh = _fake_comm(8, True)
+    assert fresh._load_tuned() and fresh.tuned == c8.tuned and fresh.tuned_ms == c8.tuned_ms
+    (tmp_path / "tune.json").write_text('{"0:25": ["nvls", 8, 4]}')          # a file of an older layout
+    assert not _fake_comm(8, True)._load_tuned()
