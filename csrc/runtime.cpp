@@ -36,7 +36,7 @@ void dlb_set_error(const char* fmt, ...) {
 }
 
 extern "C" const char* dlb_last_error(void) { return g_err; }
-extern "C" int dlb_version(void) { return 100; }
+extern "C" int dlb_version(void) { return 200; }
 
 #define RT(call)                                                                                  \
     do {                                                                                          \

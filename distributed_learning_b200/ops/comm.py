@@ -518,13 +518,16 @@ class NativeComm:
     # ---------------------------------------------------------------------------------------
     def tune(self, sizes_bytes: Sequence[int], dtype: torch.dtype = torch.float32, iters: int = 10,
              scratch_offset: int = 0, block_choices: Sequence[int] = (8, 16, 32, 48, 64),
-             unroll_choices: Sequence[int] = (4, 8), cache: bool = True) -> Dict[int, dict]:
+             unroll_choices: Sequence[int] = (2, 4), cache: bool = True) -> Dict[int, dict]:
         """Collective.  Time every available variant (grid, and pipeline depth for nvls) on each size,
         take the max over ranks, and remember the fastest per size class.  Uses arena bytes
         ``[scratch_offset, scratch_offset + 2*max(sizes))``; contents are destroyed.  With ``cache``
         the table is also read from / written to a JSON file (``$DLB200_TUNE_CACHE`` or a file in the
         temp directory named after the GPU model and the world size), so later jobs on the same box
         skip the measurement."""
+        # (pipeline depths: 4 won or tied everywhere in the 4/8-GPU sweeps and 8 lost from 16 MiB up, so 8
+        # is not tried; 2 halves the requests in flight, which is what a full 64-CTA grid -- wanted by
+        # the fused pack/SGD phases -- needs to stay near the 16-CTA optimum of the switch reduction)
         esize = torch.empty((), dtype=dtype).element_size()
         stream = torch.cuda.current_stream(self.device)
         report: Dict[int, dict] = {}
@@ -580,7 +583,8 @@ class NativeComm:
             return explicit
         gpu = re.sub(r"[^A-Za-z0-9]+", "_", torch.cuda.get_device_name(self.device))
         mc = "mc" if self.has_multicast else "nomc"
-        return os.path.join(tempfile.gettempdir(), f"dlb200_tune_{gpu}_n{self.world}_{mc}.json")
+        # the library version is part of the name: a table measured with other kernels is not reused
+        return os.path.join(tempfile.gettempdir(), f"dlb200_tune_v{lib().dlb_version()}_{gpu}_n{self.world}_{mc}.json")
 
     def _load_tuned(self) -> bool:
         """Collective: rank 0 reads the file, every rank gets the same table (or none)."""

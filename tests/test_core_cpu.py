@@ -302,3 +302,37 @@ def test_choose_heuristics_and_fused_cost_model(tmp_path, monkeypatch):
     assert fresh._load_tuned() and fresh.tuned == c8.tuned and fresh.tuned_ms == c8.tuned_ms
     (tmp_path / "tune.json").write_text('{"0:25": ["nvls", 8, 4]}')          # a file of an older layout
     assert not _fake_comm(8, True)._load_tuned()
+
+
+def test_broadcast_tensors_stages_every_byte_exactly_once():
+    """Host logic of NativeComm.broadcast_tensors with a stand-in for the kernel: the "broadcast"
+    adds 1 to every staged byte, so afterwards every byte of every tensor must be its old value + 1 --
+    whatever the arena size (chunking), tensor sizes (odd byte counts) and memory formats."""
+    from distributed_learning_b200.ops.comm import NativeComm
+
+    for cap in (64, 1000, 1 << 16):
+        c = object.__new__(NativeComm)
+        c.world, c.rank, c.data_offset = 2, 0, 32
+        c.nbytes = 32 + cap
+        c.local = torch.zeros(c.nbytes, dtype=torch.uint8)
+        calls = []
+
+        def fake_broadcast(offset, nbytes, root=0, _c=c, _calls=calls):
+            assert offset == 0 and nbytes % 16 == 0 and nbytes <= _c.nbytes - _c.data_offset
+            _c.local[_c.data_offset:_c.data_offset + nbytes] += 1
+            _calls.append(nbytes)
+
+        c.broadcast = fake_broadcast
+        torch.manual_seed(cap)
+        tensors = [torch.randint(0, 200, (n,), dtype=torch.uint8) for n in (1, 15, 16, 17, 999, 5000)]
+        tensors.append(torch.randn(3, 5, 7))
+        tensors.append(torch.randn(2, 3, 4, 5).contiguous(memory_format=torch.channels_last))   # not contiguous
+        tensors.append(torch.randn(6, 4).t())                                                   # a transposed view
+        before = [t.clone() for t in tensors]
+        moved = c.broadcast_tensors(tensors, root=0)
+        assert moved == sum(t.numel() * t.element_size() for t in tensors)
+        for t, b in zip(tensors, before):
+            got = t.contiguous().view(-1).view(torch.uint8)
+            want = b.contiguous().view(-1).view(torch.uint8) + 1
+            assert torch.equal(got, want), (cap, tuple(t.shape))
+        assert len(calls) >= (1 if cap > 20000 else 2)
