@@ -26,6 +26,30 @@ int main(void) {
     /* argument checking happens before any CUDA call, so it works without a GPU */
     if (dlb_pack(NULL, 99, NULL, NULL, NULL, NULL, 0, 1.0f, NULL) != DLB_E_ARG) return 5;
     if (strstr(dlb_last_error(), "dtype") == NULL) return 6;
+    /* round-2 entry points: descriptor form of the allreduce, named pack kernels, host-side generator */
+    {
+        dlb_allreduce_desc_t d;
+        dlb_emulated_desc_t e;
+        float a[64], b[64];
+        int64_t labels[16];
+        int i, same = 1;
+        memset(&d, 0, sizeof d);
+        memset(&e, 0, sizeof e);
+        if (dlb_allreduce(NULL, NULL) != DLB_E_ARG) return 7;
+        d.algo = 17;
+        if (dlb_allreduce(&d, NULL) != DLB_E_ARG || strstr(dlb_last_error(), "algo") == NULL) return 8;
+        d.algo = DLB_ALGO_TWOSHOT_BULK;
+        if (dlb_allreduce(&d, NULL) != DLB_E_ARG) return 9;          /* null bufs */
+        if (dlb_allreduce_emulated_ex(&e, NULL) != DLB_E_ARG) return 10;
+        if (dlb_pack_ex(NULL, DLB_F32, NULL, NULL, NULL, NULL, 0, 1.0f, 9, NULL) != DLB_E_ARG) return 11;
+        if (dlb_host_fill_uniform(a, DLB_F32, 64, 5, 1, 1) != 0 || dlb_host_fill_uniform(b, DLB_F32, 64, 5, 1, 3) != 0) return 12;
+        for (i = 0; i < 64; ++i) same = same && a[i] == b[i] && a[i] >= 0.0f && a[i] < 1.0f;
+        if (!same) return 13;                                        /* independent of the thread count */
+        if (dlb_host_fill_uniform(b, DLB_F32, 64, 5, 2, 1) != 0 || memcmp(a, b, sizeof a) == 0) return 14;
+        if (dlb_host_fill_randint(labels, 16, 10, 5, 1) != 0) return 15;
+        for (i = 0; i < 16; ++i) if (labels[i] < 0 || labels[i] >= 10) return 16;
+        if (dlb_host_fill_uniform(a, DLB_F16, 64, 5, 1, 1) != DLB_E_ARG) return 17;
+    }
     (void)dlb_device_count(&count);
     printf("ok version=%d devices=%d sgd_args=%zu bytes\n", dlb_version(), count, sizeof f);
     return 0;
